@@ -1,0 +1,52 @@
+"""Shared helpers for the parity tests (tolerances follow BASELINE.json's north_star)."""
+import functools
+import os
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+# north_star: coefficients / fitted values / RMSEP within 1e-9 relative; scores and loadings within
+# 1e-9 relative after sign normalisation; optimal_num_components exactly.
+RTOL = 1e-9
+
+
+@functools.lru_cache(maxsize=None)
+def load_golden(name):
+    with np.load(os.path.join(GOLDEN, name + ".npz")) as z:
+        return {k: z[k] for k in z.files}
+
+
+def relerr(a, b):
+    """max |a-b| / max |b| (matrix-relative, the sense in which a regression vector is 'within 1e-9')."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    den = np.abs(b).max()
+    return float(np.abs(a - b).max() / (den if den > 0 else 1.0))
+
+
+def col_relerr(a, b):
+    """worst per-column relative error (columns = components)."""
+    a = np.asarray(a); b = np.asarray(b)
+    assert a.shape == b.shape, (a.shape, b.shape)
+    den = np.abs(b).max(axis=0)
+    den[den == 0] = 1.0
+    return float((np.abs(a - b).max(axis=0) / den).max())
+
+
+def sign_normalise(state):
+    R = state["R"]
+    sg = np.sign(R[np.abs(R).argmax(axis=0), np.arange(R.shape[1])])
+    sg[sg == 0] = 1.0
+    return {k: (None if v is None else v * sg[None, :]) for k, v in state.items()}
+
+
+def assert_state_close(got, want, rtol=RTOL, keys="WPRQT"):
+    g = sign_normalise({k: got.get(k) for k in "WPRQT"})
+    w = sign_normalise({k: want.get(k) for k in "WPRQT"})
+    for k in keys:
+        if w.get(k) is None or g.get(k) is None:
+            continue
+        e = col_relerr(g[k], w[k])
+        assert e <= rtol, f"{k}: column-relative error {e:.3e} > {rtol}"
