@@ -1,0 +1,128 @@
+/* include/plsb.h — C-ABI of libplsb.so, the B200 (sm_100a) engine behind PLS::Model.
+ *
+ * The reference (tjhladish/PLS @ d976786) has no FFI layer: its boundary is the C++ API of
+ * include/PLS/pls.h, implemented on Eigen in src/pls.cpp.  This header is what a binding for the
+ * fit / predict / cross-validation path binds instead of Eigen arithmetic; every entry point cites
+ * the reference lines it replaces.  The repo's own include/PLS/pls.h + pls_b200/host/model.cpp is
+ * that binding for C++ (source-compatible PLS::Model), pls_b200/_capi.py the one for ctypes.
+ *
+ * Conventions
+ *  - plain C types only: FP64 pointers + sizes; no Eigen / torch / CUDA types cross the ABI.
+ *  - host matrices are COLUMN-MAJOR with an explicit leading dimension (Eigen's layout).
+ *  - every call returns 0 on success, non-zero on CUDA / NCCL / argument error;
+ *    plsb_last_error() then holds a message.  There is no CPU fallback: without a usable
+ *    sm_100 device every compute entry point fails with PLSB_ERR_CUDA.
+ *  - method: 0 = KERNEL_TYPE1, 1 = KERNEL_TYPE2 (pls.h:131).
+ *  - residual blocks "E" use the reference's Ev layout (pls.cpp:475, 500-507, 520):
+ *    M stacked column-major (rows x A) matrices, E[(m*A + (c-1))*rows + i].
+ */
+#ifndef PLSB_H
+#define PLSB_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PLSB_OK 0
+#define PLSB_ERR_ARG 1
+#define PLSB_ERR_CUDA 2
+#define PLSB_ERR_NCCL 3
+#define PLSB_ERR_UNSUPPORTED 4
+
+#define PLSB_KERNEL_TYPE1 0
+#define PLSB_KERNEL_TYPE2 1
+
+typedef struct plsb_ctx *plsb_ctx_t;         /* one device (+ optional communicator) */
+typedef struct plsb_dataset *plsb_dataset_t; /* device-resident X, Y (row shard of this rank) */
+
+/* ---- context ------------------------------------------------------------------------------- */
+const char *plsb_last_error(void);
+const char *plsb_version(void);
+int plsb_device_count(int *count);
+int plsb_ctx_create(int device, plsb_ctx_t *ctx);
+int plsb_ctx_destroy(plsb_ctx_t ctx);
+int plsb_ctx_sync(plsb_ctx_t ctx);
+/* Row-sharded single fits: one context per process/GPU.  Rank 0 calls
+ * plsb_comm_unique_id, the 128 bytes are broadcast by the caller's own plumbing
+ * (torch.distributed / MPI / a file), then every rank calls plsb_comm_init.  After that,
+ * plsb_fit on a dataset flagged `sharded` all-reduces the K*M / K+1 / K*K partial sums. */
+int plsb_comm_unique_id(void *id128);
+int plsb_comm_init(plsb_ctx_t ctx, int rank, int nranks, const void *id128);
+int plsb_comm_allreduce_test(plsb_ctx_t ctx, double *host_buf, int64_t n);
+
+/* ---- datasets: Model's `_X,_Y` copy (pls.cpp:344) becomes a device-resident mirror ---------- */
+/* X: N x K, Y: N x M host column-major (pinned or pageable).  Rows are this rank's shard. */
+int plsb_dataset_create(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K,
+                        const double *Y, int64_t ldy, int64_t M, plsb_dataset_t *ds);
+/* Same, but X / Y are DEVICE pointers (column-major) on ctx's device. */
+int plsb_dataset_create_device(plsb_ctx_t ctx, const double *dX, int64_t ldx, int64_t N, int64_t K,
+                               const double *dY, int64_t ldy, int64_t M, plsb_dataset_t *ds);
+/* Deterministic synthetic latent-factor data generated on the device; bit-identical
+ * to oracle/pls_oracle.c:orc_synth.  Rows [row0, row0+N) of the global data set. */
+int plsb_dataset_create_synth(plsb_ctx_t ctx, uint64_t seed, int64_t row0, int64_t N, int64_t K,
+                              int64_t M, int64_t L, plsb_dataset_t *ds);
+int plsb_dataset_destroy(plsb_dataset_t ds);
+int plsb_dataset_shape(plsb_dataset_t ds, int64_t *N, int64_t *K, int64_t *M);
+/* Copy the data set back to host column-major buffers (either may be NULL). */
+int plsb_dataset_download(plsb_dataset_t ds, double *X, int64_t ldx, double *Y, int64_t ldy);
+/* Mark the data set as one row shard of a communicator-wide fit. */
+int plsb_dataset_set_sharded(plsb_dataset_t ds, int sharded);
+
+/* ---- fit: Model::plsr (pls.cpp:390-437) ------------------------------------------------------ */
+/* Outputs (host, column-major, real parts; the reference's complex members have zero imaginary
+ * part): W,P,R are K x A, Q is M x A, T is N x A (this rank's rows; KERNEL_TYPE1 only; may be NULL). */
+int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, double *R, double *Q,
+             double *T);
+/* One-shot form taking host matrices (upload + fit), the shape Model's constructor has (pls.cpp:340-353). */
+int plsb_fit_host(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K, const double *Y,
+                  int64_t ldy, int64_t M, int64_t A, int method, double *W, double *P, double *R,
+                  double *Q, double *T);
+
+/* ---- cross products: XY = X'Y (pls.cpp:396), XX = X'X (pls.cpp:398, FP64 DMMA) -------------- */
+int plsb_xty(plsb_dataset_t ds, double *XY /* K x M col-major */);
+int plsb_xtx(plsb_dataset_t ds, double *XX /* K x K col-major, may be NULL: device only */);
+
+/* ---- prediction: scores / fitted_values / residuals / cv_NEW_DATA (pls.cpp:439-459, 494-510) -- */
+/* S = Xn * R[:, :comp]   (Nn x comp) */
+int plsb_scores(plsb_ctx_t ctx, const double *R, int64_t K, int64_t comp, const double *Xn, int64_t ldx,
+                int64_t Nn, double *S);
+/* F = Xn * (R_c Q_c')    (Nn x M);  if Yn != NULL returns residuals Yn - F instead (pls.cpp:453-455) */
+int plsb_fitted(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_t M, int64_t comp,
+                const double *Xn, int64_t ldx, int64_t Nn, const double *Yn, int64_t ldy, double *F);
+/* residuals for 1..A components in one pass: E = M stacked (Nn x A) blocks (cv_NEW_DATA layout) */
+int plsb_predict_residuals(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_t M,
+                           int64_t A, const double *Xn, int64_t ldx, int64_t Nn, const double *Yn,
+                           int64_t ldy, double *E);
+
+/* ---- cross-validation: cv_LOO (pls.cpp:469-491), cv_LSO (pls.cpp:512-549) ------------------- */
+/* nfolds folds, each leaving out test_size rows: test_idx[f*test_size + i].  The training set of a
+ * fold is the complement (cross products are order-independent up to rounding, so the reference's
+ * training-row order does not need to be shipped).  Folds [fold0, fold0+nfolds_local) are computed
+ * by this call (fold sharding across GPUs: no communication); E has `rows_total` = total folds *
+ * test_size rows per (m, c) column and only this call's rows are written. */
+int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
+                  const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E);
+
+/* ---- measurement hooks (bench.py roofline: per-kernel CUDA-event times on the launch stream) -- */
+#define PLSB_PROF_PASS_FUSED 0   /* g = X'(X r), tt, t : one streaming read of X */
+#define PLSB_PROF_PASS_XTY 1     /* S = X'Y           : one streaming read of X */
+#define PLSB_PROF_STEP 2         /* per-component single-CTA step */
+#define PLSB_PROF_XTX 3          /* DMMA X'X */
+#define PLSB_PROF_CV_GEMM 4      /* batched-fold DMMA GEMM */
+#define PLSB_PROF_CV_FOLD 5      /* per-fold small kernels */
+#define PLSB_PROF_FIT_TOTAL 6    /* whole fit, device side */
+#define PLSB_PROF_UPLOAD 7       /* H2D + layout transform */
+#define PLSB_PROF_NSLOTS 8
+int plsb_profile_enable(plsb_ctx_t ctx, int on);
+int plsb_profile_reset(plsb_ctx_t ctx);
+/* total milliseconds and launch count accumulated in a slot since the last reset */
+int plsb_profile_get(plsb_ctx_t ctx, int slot, double *ms_total, int64_t *launches);
+/* number of kernels this library launched on ctx since creation (bench.py "gpu_launches") */
+int plsb_launch_count(plsb_ctx_t ctx, int64_t *count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLSB_H */

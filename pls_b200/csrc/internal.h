@@ -1,0 +1,82 @@
+// pls_b200/csrc/internal.h — private structures and kernel launchers of libplsb.so.
+#pragma once
+#include <vector>
+
+#include "common.cuh"
+
+struct plsb_ctx {
+    int device = 0;
+    int sm_count = 148;
+    size_t smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    // scratch for cross-CTA partial sums (grown on demand)
+    double *part = nullptr;
+    size_t part_bytes = 0;
+    // communicator (lazy-loaded NCCL); rank/nranks == 0/1 when absent
+    void *comm = nullptr;
+    int rank = 0, nranks = 1;
+    // profiling
+    bool prof = false;
+    struct Pending { int slot; cudaEvent_t a, b; };
+    std::vector<Pending> pending;
+    std::vector<cudaEvent_t> pool;
+    double prof_ms[PLSB_PROF_NSLOTS] = {0};
+    int64_t prof_n[PLSB_PROF_NSLOTS] = {0};
+    int64_t launches = 0;
+};
+
+struct plsb_dataset {
+    plsb_ctx *ctx = nullptr;
+    int64_t N = 0, K = 0, M = 0;
+    int64_t ldk = 0;  // row stride of X (doubles), even, >= K, zero padded
+    int64_t ldm = 0;  // row stride of Y (doubles), even, >= M, zero padded
+    double *X = nullptr;  // row-major N x ldk
+    double *Y = nullptr;  // row-major N x ldm
+    bool sharded = false;
+};
+
+namespace plsb {
+
+int ensure_part(plsb_ctx *c, size_t bytes);
+
+// RAII-ish profiling scope: records events around a launch group when profiling is on
+struct ProfScope {
+    plsb_ctx *c;
+    int idx = -1;
+    ProfScope(plsb_ctx *ctx, int slot);
+    ~ProfScope();
+};
+
+// ---- layout transforms (pass.cu) ---------------------------------------------------------------
+// col-major src (rows x cols, ld = lds) -> row-major dst[(row0+i)*ldd + col0 + j]
+int launch_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst,
+                    int64_t ldd, int64_t col0);
+// row-major src -> col-major dst
+int launch_rm_to_cm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst,
+                    int64_t ldd);
+
+// ---- streaming passes over X (pass.cu) --------------------------------------------------------
+// out[0..ldk) = X'(X r), out[ldk] = t't, t_out[i] = (X r)_i (optional).  One read of X.
+int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out);
+// S[m*ldk + k] = sum_i X[i,k] Y[i,m]   (M x ldk, zero padded)
+int launch_xty_pass(plsb_ctx *c, const plsb_dataset *ds, double *S);
+
+// ---- per-component step (step.cu) -------------------------------------------------------------
+struct StepArgs {
+    int K, ldk, M, A;
+    int a;             // component whose pass just finished (-1: initial weight only)
+    double *S;         // M x ldk, deflated in place
+    const double *g;   // ldk + 1: X'(X r_a) and tt
+    double *W, *P, *R; // A x ldk each (column a at [a*ldk])
+    double *Q;         // A x M
+};
+int launch_step(plsb_ctx *c, const StepArgs &s);
+
+// y = G r, tt = r'G r for symmetric G (K x K, ld = ldg): KERNEL_TYPE2 per-component product
+int launch_symv(plsb_ctx *c, const double *G, int64_t ldg, int K, const double *r, double *out /*ldk+1*/, int ldk);
+
+// ---- synthetic data (synth.cu) ----------------------------------------------------------------
+int launch_synth(plsb_ctx *c, uint64_t seed, int64_t row0, int64_t N, int64_t K, int64_t M, int64_t L,
+                 double *X, int64_t ldk, double *Y, int64_t ldm);
+
+}  // namespace plsb
