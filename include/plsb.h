@@ -105,6 +105,18 @@ int plsb_predict_residuals(plsb_ctx_t ctx, const double *R, const double *Q, int
 int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
                   const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E);
 
+/* ---- host-side validation statistics (stay on the CPU: exact integer results, libstdc++ semantics) -- */
+double plsb_normalcdf(double z);                                        /* pls.cpp:152-160 */
+double plsb_wilcoxon(const double *e1, const double *e2, int64_t n);    /* pls.cpp:190-211 */
+/* out: M x A column-major; out_type 0 = RESS, 1 = MSE (pls.cpp:235-261) */
+int plsb_validation(const double *E, int64_t M, int64_t rows, int64_t A, int out_type, double *out);
+int plsb_optimal_num_components(const double *E, int64_t M, int64_t rows, int64_t A, double alpha,
+                                int64_t *out);                          /* pls.cpp:265-289 */
+/* fold lists of cv_LSO (pls.cpp:515-538, rand_nchoosek 218-227) for std::mt19937(seed);
+ * test_idx: num_trials x test_size, train_idx (may be NULL): num_trials x train_size, row-major */
+int plsb_lso_folds(int64_t N, double test_fraction, int64_t num_trials, uint32_t seed, int64_t *test_idx,
+                   int64_t *train_idx);
+
 /* ---- measurement hooks (bench.py roofline: per-kernel CUDA-event times on the launch stream) -- */
 #define PLSB_PROF_PASS_FUSED 0   /* g = X'(X r), tt, t : one streaming read of X */
 #define PLSB_PROF_PASS_XTY 1     /* S = X'Y           : one streaming read of X */

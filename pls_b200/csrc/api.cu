@@ -1,0 +1,241 @@
+// pls_b200/csrc/api.cu — C-ABI entry points of libplsb.so (include/plsb.h): context, data sets,
+// the fit driver (reference src/pls.cpp:390-437) and the measurement hooks.
+#include <dlfcn.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include <mutex>
+
+#include "internal.h"
+
+// ---- minimal NCCL surface, bound lazily with dlopen so the library loads without NCCL ------------
+typedef struct { char internal[128]; } plsb_nccl_uid;
+namespace {
+struct NcclApi {
+    void *h = nullptr;
+    int (*GetUniqueId)(plsb_nccl_uid *) = nullptr;
+    int (*CommInitRank)(void **, int, plsb_nccl_uid, int) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+} g_nccl;
+const int kNcclDouble = 8, kNcclSum = 0;  // ncclFloat64, ncclSum (nccl.h enum values, stable since 2.0)
+
+int nccl_load() {
+    if (g_nccl.h) return PLSB_OK;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) {
+        g_nccl.h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.h) break;
+    }
+    if (!g_nccl.h) { plsb::set_error("NCCL not found: %s", dlerror()); return PLSB_ERR_NCCL; }
+    g_nccl.GetUniqueId = (int (*)(plsb_nccl_uid *))dlsym(g_nccl.h, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (int (*)(void **, int, plsb_nccl_uid, int))dlsym(g_nccl.h, "ncclCommInitRank");
+    g_nccl.CommDestroy = (int (*)(void *))dlsym(g_nccl.h, "ncclCommDestroy");
+    g_nccl.AllReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(g_nccl.h, "ncclAllReduce");
+    g_nccl.GetErrorString = (const char *(*)(int))dlsym(g_nccl.h, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce) {
+        plsb::set_error("NCCL symbols missing");
+        return PLSB_ERR_NCCL;
+    }
+    return PLSB_OK;
+}
+int nccl_fail(int rc, const char *what) {
+    plsb::set_error("NCCL error %d (%s) in %s", rc, g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "?", what);
+    return PLSB_ERR_NCCL;
+}
+thread_local char g_err[1024] = "";
+}  // namespace
+
+namespace plsb {
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
+    set_error("CUDA error %d (%s) at %s:%d in %s", (int)e, cudaGetErrorString(e), file, line, what);
+    return PLSB_ERR_CUDA;
+}
+
+int ensure_part(plsb_ctx *c, size_t bytes) {
+    if (bytes <= c->part_bytes) return PLSB_OK;
+    if (c->part) {
+        PLSB_CUDA(cudaStreamSynchronize(c->stream));
+        PLSB_CUDA(cudaFree(c->part));
+        c->part = nullptr;
+        c->part_bytes = 0;
+    }
+    bytes = (size_t)round_up((int64_t)bytes, 1 << 20);
+    PLSB_CUDA(cudaMalloc(&c->part, bytes));
+    c->part_bytes = bytes;
+    return PLSB_OK;
+}
+
+ProfScope::ProfScope(plsb_ctx *ctx, int slot) : c(ctx) {
+    if (!c->prof) return;
+    plsb_ctx::Pending p;
+    p.slot = slot;
+    for (cudaEvent_t *e : {&p.a, &p.b}) {
+        if (!c->pool.empty()) { *e = c->pool.back(); c->pool.pop_back(); }
+        else if (cudaEventCreate(e) != cudaSuccess) return;
+    }
+    cudaEventRecord(p.a, c->stream);
+    c->pending.push_back(p);
+    idx = (int)c->pending.size() - 1;
+}
+ProfScope::~ProfScope() {
+    if (idx >= 0) cudaEventRecord(c->pending[idx].b, c->stream);
+}
+
+static int prof_drain(plsb_ctx *c) {
+    if (c->pending.empty()) return PLSB_OK;
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    for (auto &p : c->pending) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+            c->prof_ms[p.slot] += ms;
+            c->prof_n[p.slot] += 1;
+        }
+        c->pool.push_back(p.a);
+        c->pool.push_back(p.b);
+    }
+    c->pending.clear();
+    return PLSB_OK;
+}
+
+}  // namespace plsb
+
+using namespace plsb;
+
+extern "C" {
+
+const char *plsb_last_error(void) { return g_err; }
+const char *plsb_version(void) { return "pls_b200 0.1 (sm_100a)"; }
+
+int plsb_device_count(int *count) {
+    PLSB_ARG(count, "count is null");
+    PLSB_CUDA(cudaGetDeviceCount(count));
+    return PLSB_OK;
+}
+
+int plsb_ctx_create(int device, plsb_ctx_t *out) {
+    PLSB_ARG(out, "ctx out pointer is null");
+    int n = 0;
+    PLSB_CUDA(cudaGetDeviceCount(&n));
+    PLSB_ARG(device >= 0 && device < n, "device %d out of range (%d visible)", device, n);
+    PLSB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    PLSB_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error("device %d is sm_%d%d; libplsb.so carries sm_100a code only (no fallback)", device, prop.major, prop.minor);
+        return PLSB_ERR_UNSUPPORTED;
+    }
+    plsb_ctx *c = new plsb_ctx();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->smem_optin = prop.sharedMemPerBlockOptin;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete c; return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__); }
+    *out = c;
+    return PLSB_OK;
+}
+
+int plsb_ctx_destroy(plsb_ctx_t c) {
+    if (!c) return PLSB_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto e : c->pool) cudaEventDestroy(e);
+    if (c->part) cudaFree(c->part);
+    cudaStreamDestroy(c->stream);
+    delete c;
+    return PLSB_OK;
+}
+
+int plsb_ctx_sync(plsb_ctx_t c) {
+    PLSB_ARG(c, "ctx is null");
+    PLSB_CUDA(cudaSetDevice(c->device));
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
+}
+
+int plsb_comm_unique_id(void *id128) {
+    PLSB_ARG(id128, "id buffer is null");
+    PLSB_TRY(nccl_load());
+    plsb_nccl_uid id;
+    int rc = g_nccl.GetUniqueId(&id);
+    if (rc) return nccl_fail(rc, "ncclGetUniqueId");
+    memcpy(id128, &id, sizeof(id));
+    return PLSB_OK;
+}
+
+int plsb_comm_init(plsb_ctx_t c, int rank, int nranks, const void *id128) {
+    PLSB_ARG(c && id128, "ctx / id is null");
+    PLSB_ARG(nranks >= 1 && rank >= 0 && rank < nranks, "bad rank %d of %d", rank, nranks);
+    PLSB_TRY(nccl_load());
+    PLSB_CUDA(cudaSetDevice(c->device));
+    plsb_nccl_uid id;
+    memcpy(&id, id128, sizeof(id));
+    int rc = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+    if (rc) return nccl_fail(rc, "ncclCommInitRank");
+    c->rank = rank;
+    c->nranks = nranks;
+    return PLSB_OK;
+}
+
+int plsb_profile_enable(plsb_ctx_t c, int on) {
+    PLSB_ARG(c, "ctx is null");
+    PLSB_TRY(prof_drain(c));
+    c->prof = on != 0;
+    return PLSB_OK;
+}
+int plsb_profile_reset(plsb_ctx_t c) {
+    PLSB_ARG(c, "ctx is null");
+    PLSB_TRY(prof_drain(c));
+    for (int i = 0; i < PLSB_PROF_NSLOTS; ++i) { c->prof_ms[i] = 0; c->prof_n[i] = 0; }
+    return PLSB_OK;
+}
+int plsb_profile_get(plsb_ctx_t c, int slot, double *ms_total, int64_t *launches) {
+    PLSB_ARG(c && slot >= 0 && slot < PLSB_PROF_NSLOTS, "bad profile slot");
+    PLSB_TRY(prof_drain(c));
+    if (ms_total) *ms_total = c->prof_ms[slot];
+    if (launches) *launches = c->prof_n[slot];
+    return PLSB_OK;
+}
+int plsb_launch_count(plsb_ctx_t c, int64_t *count) {
+    PLSB_ARG(c && count, "null argument");
+    *count = c->launches;
+    return PLSB_OK;
+}
+
+}  // extern "C"
+
+// allreduce helper used by the fit driver (sum of FP64 partials across the row shards)
+namespace plsb {
+int allreduce_sum(plsb_ctx *c, double *buf, size_t n) {
+    if (c->nranks <= 1 || !c->comm) return PLSB_OK;
+    int rc = g_nccl.AllReduce(buf, buf, n, kNcclDouble, kNcclSum, c->comm, c->stream);
+    if (rc) return nccl_fail(rc, "ncclAllReduce");
+    return PLSB_OK;
+}
+}  // namespace plsb
+
+extern "C" int plsb_comm_allreduce_test(plsb_ctx_t c, double *host_buf, int64_t n) {
+    PLSB_ARG(c && host_buf && n > 0, "bad argument");
+    PLSB_CUDA(cudaSetDevice(c->device));
+    double *d = nullptr;
+    PLSB_CUDA(cudaMalloc(&d, sizeof(double) * n));
+    PLSB_CUDA(cudaMemcpyAsync(d, host_buf, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
+    int rc = plsb::allreduce_sum(c, d, (size_t)n);
+    if (rc == PLSB_OK) {
+        cudaError_t e = cudaMemcpyAsync(host_buf, d, sizeof(double) * n, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "allreduce_test copy", __FILE__, __LINE__);
+    }
+    cudaFree(d);
+    return rc;
+}

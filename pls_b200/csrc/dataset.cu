@@ -1,0 +1,153 @@
+// pls_b200/csrc/dataset.cu — device-resident data sets: the role of Model's `_X,_Y` copies
+// (reference src/pls.cpp:344, include/PLS/pls.h:251), kept in HBM in the row-major layout the
+// streaming passes want.
+#include "internal.h"
+
+namespace plsb {
+
+int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst, int64_t ldd,
+                    bool src_on_device) {
+    if (rows == 0 || cols == 0) return PLSB_OK;
+    if (src_on_device) return launch_cm_to_rm(c, src, lds, rows, cols, dst, ldd, 0);
+    // stage column blocks of <= 256 MB through one device buffer; the transpose runs at HBM speed,
+    // so the copy engine is the only thing that matters here
+    int64_t kc = (int64_t)(256u << 20) / (rows * 8);
+    if (kc < 1) kc = 1;
+    if (kc > cols) kc = cols;
+    double *stage = nullptr;
+    PLSB_CUDA(cudaMalloc(&stage, (size_t)rows * kc * sizeof(double)));
+    int rc = PLSB_OK;
+    for (int64_t c0 = 0; c0 < cols && rc == PLSB_OK; c0 += kc) {
+        const int64_t nc = cols - c0 < kc ? cols - c0 : kc;
+        cudaError_t e = cudaMemcpy2DAsync(stage, (size_t)rows * 8, src + c0 * lds, (size_t)lds * 8, (size_t)rows * 8,
+                                          (size_t)nc, cudaMemcpyHostToDevice, c->stream);
+        if (e != cudaSuccess) { rc = cuda_fail(e, "cudaMemcpy2DAsync(H2D)", __FILE__, __LINE__); break; }
+        rc = launch_cm_to_rm(c, stage, rows, rows, nc, dst, ldd, c0);
+    }
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (rc == PLSB_OK && e != cudaSuccess) rc = cuda_fail(e, "upload sync", __FILE__, __LINE__);
+    cudaFree(stage);
+    return rc;
+}
+
+static int dataset_alloc(plsb_ctx *c, int64_t N, int64_t K, int64_t M, plsb_dataset **out) {
+    PLSB_ARG(c && out, "null argument");
+    PLSB_ARG(N >= 0 && K >= 1 && M >= 1, "bad shape N=%lld K=%lld M=%lld", (long long)N, (long long)K, (long long)M);
+    PLSB_CUDA(cudaSetDevice(c->device));
+    plsb_dataset *ds = new plsb_dataset();
+    ds->ctx = c; ds->N = N; ds->K = K; ds->M = M;
+    ds->ldk = round_up(K, 2);
+    ds->ldm = round_up(M, 2);
+    const size_t nx = (size_t)(N > 0 ? N : 1) * ds->ldk, ny = (size_t)(N > 0 ? N : 1) * ds->ldm;
+    cudaError_t e = cudaMalloc(&ds->X, nx * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&ds->Y, ny * sizeof(double));
+    if (e == cudaSuccess && ds->ldk != K) e = cudaMemsetAsync(ds->X, 0, nx * sizeof(double), c->stream);
+    if (e == cudaSuccess && ds->ldm != M) e = cudaMemsetAsync(ds->Y, 0, ny * sizeof(double), c->stream);
+    if (e != cudaSuccess) {
+        if (ds->X) cudaFree(ds->X);
+        if (ds->Y) cudaFree(ds->Y);
+        delete ds;
+        return cuda_fail(e, "dataset alloc", __FILE__, __LINE__);
+    }
+    *out = ds;
+    return PLSB_OK;
+}
+
+static int dataset_fill(plsb_ctx *c, const double *X, int64_t ldx, int64_t N, int64_t K, const double *Y, int64_t ldy,
+                        int64_t M, bool on_device, plsb_dataset_t *out) {
+    PLSB_ARG(N == 0 || (X && Y), "X / Y is null");
+    PLSB_ARG(ldx >= N && ldy >= N, "leading dimension smaller than N");
+    plsb_dataset *ds = nullptr;
+    PLSB_TRY(dataset_alloc(c, N, K, M, &ds));
+    int rc;
+    {
+        ProfScope ps(c, PLSB_PROF_UPLOAD);
+        rc = upload_cm_to_rm(c, X, ldx, N, K, ds->X, ds->ldk, on_device);
+        if (rc == PLSB_OK) rc = upload_cm_to_rm(c, Y, ldy, N, M, ds->Y, ds->ldm, on_device);
+    }
+    if (rc != PLSB_OK) { plsb_dataset_destroy(ds); return rc; }
+    *out = ds;
+    return PLSB_OK;
+}
+
+}  // namespace plsb
+
+using namespace plsb;
+
+extern "C" {
+
+int plsb_dataset_create(plsb_ctx_t c, const double *X, int64_t ldx, int64_t N, int64_t K, const double *Y,
+                        int64_t ldy, int64_t M, plsb_dataset_t *ds) {
+    return dataset_fill(c, X, ldx, N, K, Y, ldy, M, false, ds);
+}
+int plsb_dataset_create_device(plsb_ctx_t c, const double *dX, int64_t ldx, int64_t N, int64_t K, const double *dY,
+                               int64_t ldy, int64_t M, plsb_dataset_t *ds) {
+    return dataset_fill(c, dX, ldx, N, K, dY, ldy, M, true, ds);
+}
+int plsb_dataset_create_synth(plsb_ctx_t c, uint64_t seed, int64_t row0, int64_t N, int64_t K, int64_t M, int64_t L,
+                              plsb_dataset_t *out) {
+    plsb_dataset *ds = nullptr;
+    PLSB_TRY(dataset_alloc(c, N, K, M, &ds));
+    int rc = launch_synth(c, seed, row0, N, K, M, L, ds->X, ds->ldk, ds->Y, ds->ldm);
+    if (rc == PLSB_OK) {
+        cudaError_t e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "synth", __FILE__, __LINE__);
+    }
+    if (rc != PLSB_OK) { plsb_dataset_destroy(ds); return rc; }
+    *out = ds;
+    return PLSB_OK;
+}
+int plsb_dataset_destroy(plsb_dataset_t ds) {
+    if (!ds) return PLSB_OK;
+    cudaSetDevice(ds->ctx->device);
+    cudaStreamSynchronize(ds->ctx->stream);
+    if (ds->X) cudaFree(ds->X);
+    if (ds->Y) cudaFree(ds->Y);
+    delete ds;
+    return PLSB_OK;
+}
+int plsb_dataset_shape(plsb_dataset_t ds, int64_t *N, int64_t *K, int64_t *M) {
+    PLSB_ARG(ds, "dataset is null");
+    if (N) *N = ds->N;
+    if (K) *K = ds->K;
+    if (M) *M = ds->M;
+    return PLSB_OK;
+}
+int plsb_dataset_set_sharded(plsb_dataset_t ds, int sharded) {
+    PLSB_ARG(ds, "dataset is null");
+    ds->sharded = sharded != 0;
+    return PLSB_OK;
+}
+
+static int download_rm_to_cm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst,
+                             int64_t ldd) {
+    if (rows == 0 || cols == 0) return PLSB_OK;
+    int64_t kc = (int64_t)(256u << 20) / (rows * 8);
+    if (kc < 1) kc = 1;
+    if (kc > cols) kc = cols;
+    double *stage = nullptr;
+    PLSB_CUDA(cudaMalloc(&stage, (size_t)rows * kc * sizeof(double)));
+    int rc = PLSB_OK;
+    for (int64_t c0 = 0; c0 < cols && rc == PLSB_OK; c0 += kc) {
+        const int64_t nc = cols - c0 < kc ? cols - c0 : kc;
+        rc = launch_rm_to_cm(c, src + c0, lds, rows, nc, stage, rows);
+        if (rc != PLSB_OK) break;
+        cudaError_t e = cudaMemcpy2DAsync(dst + c0 * ldd, (size_t)ldd * 8, stage, (size_t)rows * 8, (size_t)rows * 8,
+                                          (size_t)nc, cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy2DAsync(D2H)", __FILE__, __LINE__);
+    }
+    cudaFree(stage);
+    return rc;
+}
+
+int plsb_dataset_download(plsb_dataset_t ds, double *X, int64_t ldx, double *Y, int64_t ldy) {
+    PLSB_ARG(ds, "dataset is null");
+    plsb_ctx *c = ds->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    if (X) { PLSB_ARG(ldx >= ds->N, "ldx < N"); PLSB_TRY(download_rm_to_cm(c, ds->X, ds->ldk, ds->N, ds->K, X, ldx)); }
+    if (Y) { PLSB_ARG(ldy >= ds->N, "ldy < N"); PLSB_TRY(download_rm_to_cm(c, ds->Y, ds->ldm, ds->N, ds->M, Y, ldy)); }
+    return PLSB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,130 @@
+// pls_b200/csrc/fit.cu — the fit driver: Model::plsr (reference src/pls.cpp:390-437) on the device.
+//
+// KERNEL_TYPE1:  S = X'Y (one pass) ; per component: ONE fused pass g = X'(X r), tt = |X r|^2, t = X r,
+//                then the single-CTA step (p, q, deflation of S, next w and r).
+// KERNEL_TYPE2:  additionally XX = X'X once (FP64 DMMA), per component g = XX r, tt = r'g.
+// Row-sharded fits all-reduce S (K*M), XX (K*K) once and [g | tt] (K+1 doubles) per component.
+#include "internal.h"
+
+namespace plsb {
+
+struct DevBuf {
+    plsb_ctx *c;
+    double *p = nullptr;
+    explicit DevBuf(plsb_ctx *ctx) : c(ctx) {}
+    int alloc(size_t n, bool zero) {
+        PLSB_CUDA(cudaMallocAsync(&p, (n ? n : 1) * sizeof(double), c->stream));
+        if (zero) PLSB_CUDA(cudaMemsetAsync(p, 0, (n ? n : 1) * sizeof(double), c->stream));
+        return PLSB_OK;
+    }
+    ~DevBuf() { if (p) cudaFreeAsync(p, c->stream); }
+};
+
+int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg);  // gemm.cu
+
+// device-side fit; outputs stay on the device (A x ldk / A x M / A x N, "component-major")
+int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, double *Rd, double *Qd, double *Td) {
+    plsb_ctx *c = ds->ctx;
+    const int64_t K = ds->K, ldk = ds->ldk, M = ds->M;
+    const bool shard = ds->sharded && c->nranks > 1;
+    ProfScope total(c, PLSB_PROF_FIT_TOTAL);
+    DevBuf S(c), g(c), G(c);
+    PLSB_TRY(S.alloc((size_t)M * ldk, false));
+    PLSB_TRY(g.alloc((size_t)ldk + 2, true));
+    PLSB_TRY(launch_xty_pass(c, ds, S.p));
+    if (shard) PLSB_TRY(allreduce_sum(c, S.p, (size_t)M * ldk));
+    const int64_t ldg = round_up(K, 2);
+    if (method == PLSB_KERNEL_TYPE2) {
+        PLSB_TRY(G.alloc((size_t)K * ldg, true));
+        PLSB_TRY(launch_xtx(c, ds, G.p, ldg));
+        if (shard) PLSB_TRY(allreduce_sum(c, G.p, (size_t)K * ldg));
+    }
+    StepArgs st{};
+    st.K = (int)K; st.ldk = (int)ldk; st.M = (int)M; st.A = (int)A;
+    st.S = S.p; st.g = g.p; st.W = Wd; st.P = Pd; st.R = Rd; st.Q = Qd;
+    st.a = -1;
+    PLSB_TRY(launch_step(c, st));
+    for (int64_t a = 0; a < A; ++a) {
+        const double *r = Rd + a * ldk;
+        if (method == PLSB_KERNEL_TYPE1) {
+            PLSB_TRY(launch_fused_pass(c, ds, r, g.p, Td ? Td + a * ds->N : nullptr));
+            if (shard) PLSB_TRY(allreduce_sum(c, g.p, (size_t)ldk + 1));
+        } else {
+            PLSB_TRY(launch_symv(c, G.p, ldg, (int)K, r, g.p, (int)ldk));
+        }
+        st.a = (int)a;
+        PLSB_TRY(launch_step(c, st));
+    }
+    return PLSB_OK;
+}
+
+}  // namespace plsb
+
+using namespace plsb;
+
+extern "C" {
+
+int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, double *R, double *Q, double *T) {
+    PLSB_ARG(ds, "dataset is null");
+    PLSB_ARG(A >= 1, "A must be >= 1");
+    PLSB_ARG(method == PLSB_KERNEL_TYPE1 || method == PLSB_KERNEL_TYPE2, "unknown method %d", method);
+    plsb_ctx *c = ds->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    const int64_t K = ds->K, ldk = ds->ldk, M = ds->M, N = ds->N;
+    DevBuf Wd(c), Pd(c), Rd(c), Qd(c), Td(c);
+    PLSB_TRY(Wd.alloc((size_t)A * ldk, true));
+    PLSB_TRY(Pd.alloc((size_t)A * ldk, true));
+    PLSB_TRY(Rd.alloc((size_t)A * ldk, true));
+    PLSB_TRY(Qd.alloc((size_t)A * M, true));
+    const bool wantT = T != nullptr && method == PLSB_KERNEL_TYPE1 && N > 0;
+    if (wantT) PLSB_TRY(Td.alloc((size_t)A * N, false));
+    PLSB_TRY(fit_device(ds, A, method, Wd.p, Pd.p, Rd.p, Qd.p, wantT ? Td.p : nullptr));
+    const size_t kb = (size_t)K * sizeof(double), lb = (size_t)ldk * sizeof(double);
+    if (W) PLSB_CUDA(cudaMemcpy2DAsync(W, kb, Wd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
+    if (P) PLSB_CUDA(cudaMemcpy2DAsync(P, kb, Pd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
+    if (R) PLSB_CUDA(cudaMemcpy2DAsync(R, kb, Rd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
+    if (Q) PLSB_CUDA(cudaMemcpyAsync(Q, Qd.p, (size_t)A * M * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (wantT) PLSB_CUDA(cudaMemcpyAsync(T, Td.p, (size_t)A * N * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
+}
+
+int plsb_fit_host(plsb_ctx_t c, const double *X, int64_t ldx, int64_t N, int64_t K, const double *Y, int64_t ldy,
+                  int64_t M, int64_t A, int method, double *W, double *P, double *R, double *Q, double *T) {
+    plsb_dataset_t ds = nullptr;
+    PLSB_TRY(plsb_dataset_create(c, X, ldx, N, K, Y, ldy, M, &ds));
+    int rc = plsb_fit(ds, A, method, W, P, R, Q, T);
+    plsb_dataset_destroy(ds);
+    return rc;
+}
+
+int plsb_xty(plsb_dataset_t ds, double *XY) {
+    PLSB_ARG(ds && XY, "null argument");
+    plsb_ctx *c = ds->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    DevBuf S(c);
+    PLSB_TRY(S.alloc((size_t)ds->M * ds->ldk, false));
+    PLSB_TRY(launch_xty_pass(c, ds, S.p));
+    if (ds->sharded && c->nranks > 1) PLSB_TRY(allreduce_sum(c, S.p, (size_t)ds->M * ds->ldk));
+    PLSB_CUDA(cudaMemcpy2DAsync(XY, (size_t)ds->K * 8, S.p, (size_t)ds->ldk * 8, (size_t)ds->K * 8, (size_t)ds->M,
+                                cudaMemcpyDeviceToHost, c->stream));
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
+}
+
+int plsb_xtx(plsb_dataset_t ds, double *XX) {
+    PLSB_ARG(ds, "null argument");
+    plsb_ctx *c = ds->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    const int64_t K = ds->K, ldg = round_up(K, 2);
+    DevBuf G(c);
+    PLSB_TRY(G.alloc((size_t)K * ldg, false));
+    PLSB_TRY(launch_xtx(c, ds, G.p, ldg));
+    if (ds->sharded && c->nranks > 1) PLSB_TRY(allreduce_sum(c, G.p, (size_t)K * ldg));
+    if (XX) PLSB_CUDA(cudaMemcpy2DAsync(XX, (size_t)K * 8, G.p, (size_t)ldg * 8, (size_t)K * 8, (size_t)K,
+                                        cudaMemcpyDeviceToHost, c->stream));
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,183 @@
+// pls_b200/csrc/gemm.cu — FP64 tensor-core (DMMA) contraction C = A' B over a long reduction axis.
+//
+// Replaces XX = X' * X (reference src/pls.cpp:398; Eigen GEBP there) and serves the batched-fold
+// product XX * R_batch of the cross-validation engine.  Operands are "k-major": A is Kd x M and B is
+// Kd x N, both row-major (the reduction index is the slow one), which is exactly how X (rows = samples)
+// and the fold-minor vector batches sit in HBM.  FP64 has no tcgen05 kind on sm_100a: the tensor path
+// is warp-level mma.sync m8n8k4 (SASS DMMA), fed from shared memory tiles staged with cp.async.
+//
+// Split-K over the reduction axis fills the 148 SMs; partial tiles go to scratch and are summed in
+// split order by a second kernel (no atomics: deterministic).  SYRK mode computes only tiles on or
+// above the diagonal and mirrors them.
+#include "internal.h"
+
+namespace plsb {
+
+constexpr int GM_BM = 128, GM_BN = 128, GM_BK = 16, GM_LD = 132, GM_NT = 256, GM_STAGES = 3;
+
+struct GemmArgs {
+    const double *A; int64_t lda;   // Kd x M
+    const double *B; int64_t ldb;   // Kd x N
+    int64_t Kd; int M, N;
+    int tiles_m, tiles_n, ntiles, splitk;
+    int64_t k_per_split;            // multiple of GM_BK
+    double *part;                   // [splitk][ntiles][BM*BN]
+    int syrk;
+};
+
+__device__ __forceinline__ void cp_async16(void *dst, const void *src, bool pred) {
+    const int sz = pred ? 16 : 0;
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst)), "l"(src), "r"(sz) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+// map a linear SYRK tile index to (tm, tn) with tn >= tm
+__device__ __forceinline__ void syrk_tile(int t, int T, int &tm, int &tn) {
+    int row = 0;
+    while (t >= T - row) { t -= T - row; ++row; }
+    tm = row; tn = row + t;
+}
+
+__global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
+    extern __shared__ __align__(128) char smem[];
+    double *As = reinterpret_cast<double *>(smem);                       // [STAGES][BK][LD]
+    double *Bs = As + (size_t)GM_STAGES * GM_BK * GM_LD;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x % g.ntiles, split = blockIdx.x / g.ntiles;
+    int tm, tn;
+    if (g.syrk) syrk_tile(tile, g.tiles_m, tm, tn);
+    else { tm = tile / g.tiles_n; tn = tile % g.tiles_n; }
+    const int m_base = tm * GM_BM, n_base = tn * GM_BN;
+    const int64_t k_begin = (int64_t)split * g.k_per_split;
+    int64_t k_end = k_begin + g.k_per_split;
+    if (k_end > g.Kd) k_end = g.Kd;
+    const int nk = k_begin < k_end ? (int)((k_end - k_begin + GM_BK - 1) / GM_BK) : 0;
+
+    auto load_stage = [&](int st, int kt) {
+        const int64_t k0 = k_begin + (int64_t)kt * GM_BK;
+#pragma unroll
+        for (int i = 0; i < (GM_BK * GM_BM / 2) / GM_NT; ++i) {
+            const int ch = tid + i * GM_NT;        // 16-byte chunk id in the BK x 128 tile
+            const int kr = ch / (GM_BM / 2), cc = (ch % (GM_BM / 2)) * 2;
+            const int64_t k = k0 + kr;
+            const bool kin = k < k_end;
+            const bool pa = kin && (m_base + cc) < g.M, pb = kin && (n_base + cc) < g.N;
+            cp_async16(As + ((size_t)st * GM_BK + kr) * GM_LD + cc, pa ? g.A + k * g.lda + m_base + cc : g.A, pa);
+            cp_async16(Bs + ((size_t)st * GM_BK + kr) * GM_LD + cc, pb ? g.B + k * g.ldb + n_base + cc : g.B, pb);
+        }
+    };
+
+    double acc[8][4][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+
+    for (int s = 0; s < GM_STAGES - 1; ++s) {
+        if (s < nk) load_stage(s, s);
+        cp_async_commit();
+    }
+    const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;
+    const int fk = lane & 3, fr = lane >> 2;
+    for (int kt = 0; kt < nk; ++kt) {
+        cp_async_wait<GM_STAGES - 2>();
+        __syncthreads();
+        {   // prefetch the tile STAGES-1 ahead into the slot freed in the previous iteration
+            const int nx = kt + GM_STAGES - 1;
+            if (nx < nk) load_stage(nx % GM_STAGES, nx);
+            cp_async_commit();
+        }
+        const double *as = As + (size_t)(kt % GM_STAGES) * GM_BK * GM_LD;
+        const double *bs = Bs + (size_t)(kt % GM_STAGES) * GM_BK * GM_LD;
+#pragma unroll
+        for (int kk = 0; kk < GM_BK / 4; ++kk) {
+            double a[8], b[4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = as[(kk * 4 + fk) * GM_LD + wm + i * 8 + fr];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bs[(kk * 4 + fk) * GM_LD + wn + j * 8 + fr];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+        }
+    }
+    cp_async_wait<0>();
+    double *out = g.part + ((size_t)split * g.ntiles + tile) * (GM_BM * GM_BN);
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int row = wm + i * 8 + fr, col = wn + j * 8 + fk * 2;
+            *reinterpret_cast<double2 *>(out + row * GM_BN + col) = make_double2(acc[i][j][0], acc[i][j][1]);
+        }
+}
+
+// C[m*ldc + n] = sum_s part[s][tile][...]; SYRK also writes the mirrored element
+__global__ void __launch_bounds__(256) gemm_reduce_kernel(const GemmArgs g, double *__restrict__ C, int64_t ldc) {
+    const int tile = blockIdx.x;
+    int tm, tn;
+    if (g.syrk) syrk_tile(tile, g.tiles_m, tm, tn);
+    else { tm = tile / g.tiles_n; tn = tile % g.tiles_n; }
+    for (int e = threadIdx.x; e < GM_BM * GM_BN; e += 256) {
+        const int row = e / GM_BN, col = e % GM_BN;
+        const int m = tm * GM_BM + row, n = tn * GM_BN + col;
+        if (m >= g.M || n >= g.N) continue;
+        double s = 0.0;
+        for (int sp = 0; sp < g.splitk; ++sp) s += g.part[((size_t)sp * g.ntiles + tile) * (GM_BM * GM_BN) + e];
+        C[(int64_t)m * ldc + n] = s;
+        if (g.syrk && tm != tn) C[(int64_t)n * ldc + m] = s;
+    }
+}
+
+// C (M x N, row-major, ldc) = A' B.  syrk: A == B, M == N, C symmetric.
+int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
+                    double *C, int64_t ldc, bool syrk, int prof_slot) {
+    if (M == 0 || N == 0) return PLSB_OK;
+    PLSB_ARG((lda % 2) == 0 && (ldb % 2) == 0, "gemm: leading dimensions must be even");
+    GemmArgs g{};
+    g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.Kd = Kd; g.M = M; g.N = N; g.syrk = syrk ? 1 : 0;
+    g.tiles_m = (int)ceil_div(M, GM_BM);
+    g.tiles_n = (int)ceil_div(N, GM_BN);
+    g.ntiles = syrk ? g.tiles_m * (g.tiles_m + 1) / 2 : g.tiles_m * g.tiles_n;
+    // enough CTAs for ~4 waves, but at least 64 k-steps per split
+    int64_t want = ceil_div((int64_t)4 * c->sm_count, g.ntiles);
+    int64_t maxsplit = ceil_div(Kd, (int64_t)GM_BK * 64);
+    if (want > maxsplit) want = maxsplit;
+    if (want < 1) want = 1;
+    g.k_per_split = round_up(ceil_div(Kd > 0 ? Kd : 1, want), GM_BK);
+    g.splitk = (int)ceil_div(Kd > 0 ? Kd : 1, g.k_per_split);
+    const size_t pbytes = (size_t)g.splitk * g.ntiles * GM_BM * GM_BN * sizeof(double);
+    PLSB_TRY(ensure_part(c, pbytes));
+    g.part = c->part;
+    const size_t smem = (size_t)2 * GM_STAGES * GM_BK * GM_LD * sizeof(double);
+    PLSB_CUDA(cudaFuncSetAttribute(dmma_atb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        ProfScope ps(c, prof_slot);
+        dmma_atb_kernel<<<(unsigned)(g.ntiles * g.splitk), GM_NT, smem, c->stream>>>(g);
+    }
+    PLSB_CUDA(cudaGetLastError());
+    gemm_reduce_kernel<<<(unsigned)g.ntiles, 256, 0, c->stream>>>(g, C, ldc);
+    PLSB_CUDA(cudaGetLastError());
+    c->launches += 2;
+    return PLSB_OK;
+}
+
+int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg) {
+    if (ds->N == 0) {
+        PLSB_CUDA(cudaMemsetAsync(G, 0, (size_t)ds->K * ldg * sizeof(double), c->stream));
+        return PLSB_OK;
+    }
+    return launch_gemm_atb(c, ds->X, ds->ldk, ds->X, ds->ldk, ds->N, (int)ds->K, (int)ds->K, G, ldg, true,
+                           PLSB_PROF_XTX);
+}
+
+}  // namespace plsb

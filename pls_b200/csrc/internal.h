@@ -38,6 +38,11 @@ struct plsb_dataset {
 namespace plsb {
 
 int ensure_part(plsb_ctx *c, size_t bytes);
+// in-place sum across the communicator's ranks on c->stream (no-op without a communicator)
+int allreduce_sum(plsb_ctx *c, double *buf, size_t n);
+// upload a host column-major matrix into a device row-major one (staged, chunked by columns)
+int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst, int64_t ldd,
+                    bool src_on_device);
 
 // RAII-ish profiling scope: records events around a launch group when profiling is on
 struct ProfScope {

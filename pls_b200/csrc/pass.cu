@@ -412,7 +412,10 @@ static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, doubl
     a.part = c->part;
     auto kern = fused_pass_kernel<NT, TPR, VEC, RB>;
     PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)grid, NT, smem, c->stream>>>(a);
+    {
+        ProfScope ps(c, PLSB_PROF_PASS_FUSED);
+        kern<<<(unsigned)grid, NT, smem, c->stream>>>(a);
+    }
     PLSB_CUDA(cudaGetLastError());
     reduce_partials_kernel<<<(unsigned)ceil_div(a.ldk + 1, 256), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid,
                                                                                        a.ldk + 1, out);
@@ -478,7 +481,10 @@ static int run_xty(plsb_ctx *c, const plsb_dataset *ds, double *S) {
     for (int m0 = 0; m0 < ds->M; m0 += MC) {
         a.m0 = m0;
         a.mc = (int)(ds->M - m0 < MC ? ds->M - m0 : MC);
-        kern<<<(unsigned)grid, NT, smem, c->stream>>>(a);
+        {
+            ProfScope ps(c, PLSB_PROF_PASS_XTY);
+            kern<<<(unsigned)grid, NT, smem, c->stream>>>(a);
+        }
         PLSB_CUDA(cudaGetLastError());
         const int64_t len = (int64_t)a.mc * a.ldk;
         reduce_partials_kernel<<<(unsigned)ceil_div(len, 256), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid, len,

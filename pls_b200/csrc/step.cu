@@ -137,7 +137,10 @@ int launch_step(plsb_ctx *c, const StepArgs &s) {
         set_error("M=%d responses exceed the in-kernel eigen solver limit (%d)", s.M, PLSB_MAX_M);
         return PLSB_ERR_UNSUPPORTED;
     }
-    step_kernel<<<1, STEP_NT, 0, c->stream>>>(s);
+    {
+        ProfScope ps(c, PLSB_PROF_STEP);
+        step_kernel<<<1, STEP_NT, 0, c->stream>>>(s);
+    }
     c->launches++;
     PLSB_CUDA(cudaGetLastError());
     return PLSB_OK;
