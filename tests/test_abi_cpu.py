@@ -1,0 +1,56 @@
+"""CPU-side checks of the drop-in boundary: libplsb.so loads, exports every symbol include/plsb.h
+declares, fails loudly without a device, and its host-side statistics (validation, Wilcoxon,
+optimal_num_components, LSO fold lists) reproduce the reference's golden vectors."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from pls_b200 import _capi
+from tests.util import RTOL, load_golden, relerr
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_exported():
+    hdr = open(os.path.join(ROOT, "include", "plsb.h")).read()
+    declared = set(re.findall(r"\b(plsb_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"plsb_ctx", "plsb_dataset"}
+    assert declared, "no declarations parsed"
+    lib = _capi.lib()
+    missing = [s for s in sorted(declared) if not hasattr(lib, s)]
+    assert not missing, f"libplsb.so does not export: {missing}"
+    assert set(_capi.SYMBOLS) == declared
+
+
+def test_no_cpu_fallback_without_device():
+    import ctypes as C
+    n = C.c_int(-1)
+    rc = _capi.lib().plsb_device_count(C.byref(n))
+    if rc == 0 and n.value > 0:
+        pytest.skip("a CUDA device is visible")
+    with pytest.raises(_capi.PlsbError):
+        _capi.Context(0)
+
+
+def test_host_stats_match_reference_goldens():
+    s = load_golden("stats")
+    assert np.allclose([_capi.normalcdf(z) for z in s["z"]], s["cdf"], rtol=0, atol=1e-15)
+    assert np.allclose([_capi.wilcoxon(a, b) for a, b in zip(s["e1"], s["e2"])], s["wil"], rtol=0, atol=1e-14)
+    g = load_golden("c2_nir_octane")
+    assert relerr(_capi.validation(g["loo"], 0), g["loo_ress"]) <= RTOL
+    assert relerr(_capi.validation(g["loo"], 1), g["loo_mse"]) <= RTOL
+    assert np.array_equal(_capi.optimal_num_components(g["loo"]), g["loo_opt"])
+    g = load_golden("c1_toy")
+    assert np.array_equal(_capi.optimal_num_components(g["loo"]), g["loo_opt"])
+    assert np.array_equal(_capi.optimal_num_components(g["lso"]), g["lso_opt"])
+    assert relerr(_capi.validation(g["lso"], 1), g["lso_mse"]) <= RTOL
+
+
+@pytest.mark.parametrize("name,N,trials", [("c1_toy", 10, 100), ("c2_nir_octane", 60, 600), ("c3_nir_pls2", 60, 1000)])
+def test_lso_folds_match_reference(name, N, trials):
+    g = load_golden(name)
+    tr, te = _capi.lso_folds(N, 0.3, trials)          # std::mt19937 default seed, like main.cpp:38
+    assert np.array_equal(tr, g["lso_train"].astype(np.int64))
+    assert np.array_equal(te, g["lso_test"].astype(np.int64))

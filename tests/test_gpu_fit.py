@@ -1,0 +1,144 @@
+"""Parity of the CUDA fit / predict path (through the C-ABI) with the reference: committed golden
+vectors produced by the unmodified reference, and the CPU oracle on seeded inputs.  Tolerances are the
+north star's: 1e-9 relative (scores / loadings after sign normalisation)."""
+import numpy as np
+import pytest
+
+from oracle import port
+from pls_b200 import _capi
+from tests.util import RTOL, assert_state_close, load_golden, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = _capi.Context(0)
+    yield c
+    c.close()
+
+
+def test_synth_is_bit_identical_to_oracle(ctx):
+    for (seed, N, K, M, L, row0) in [(123, 1000, 77, 3, 16, 0), (20260004, 300, 256, 8, 16, 4096), (5, 33, 15, 1, 4, 7)]:
+        ds = _capi.Dataset(ctx, synth=(seed, row0, N, K, M, L))
+        X, Y = ds.download()
+        Xo, Yo = port.synth(seed, row0 + N, K, M, L=L, row0=row0, rows=N)
+        assert np.array_equal(X, Xo) and np.array_equal(Y, Yo)
+        ds.close()
+
+
+def test_upload_download_roundtrip(ctx):
+    rng = np.random.default_rng(0)
+    for N, K, M in [(1, 1, 1), (37, 15, 2), (513, 203, 3), (64, 1025, 8)]:
+        X = np.asfortranarray(rng.standard_normal((N, K))); Y = np.asfortranarray(rng.standard_normal((N, M)))
+        ds = _capi.Dataset(ctx, X, Y)
+        X2, Y2 = ds.download()
+        assert np.array_equal(X, X2) and np.array_equal(Y, Y2)
+        ds.close()
+
+
+@pytest.mark.parametrize("name,A", [("c1_toy", 2), ("c2_nir_octane", 10), ("c3_nir_pls2", 10)])
+@pytest.mark.parametrize("method", [0, 1])
+def test_fit_matches_reference_golden(ctx, name, A, method):
+    g = load_golden(name)
+    pre = "" if method == 0 else "t2_"
+    ds = _capi.Dataset(ctx, g["X"], g["Y"])
+    st = ds.fit(A, method)
+    assert_state_close(st, {k: g.get(pre + k) for k in "WPRQT"})
+    R, Q = st["R"], st["Q"]
+    B = _capi.fitted(ctx, R, Q, A, np.eye(R.shape[0]))
+    assert relerr(B, g[pre + "coef_A"]) <= RTOL
+    assert relerr(_capi.fitted(ctx, R, Q, 1, np.eye(R.shape[0])), g[pre + "coef_1"]) <= RTOL
+    assert relerr(_capi.fitted(ctx, R, Q, A, g["X"]), g[pre + "fitted_A"]) <= RTOL
+    sse = np.array([(_capi.fitted(ctx, R, Q, c, g["X"], g["Y"]) ** 2).sum(axis=0) for c in range(1, A + 1)])
+    assert relerr(sse, g[pre + "sse"]) <= 1e-8
+    sc = _capi.scores(ctx, R, A, g["X"])
+    sgn = np.sign((sc * g[pre + "scores_A"]).sum(axis=0))
+    assert relerr(sc * sgn, g[pre + "scores_A"]) <= RTOL
+    ds.close()
+
+
+@pytest.mark.parametrize("name", ["c4s", "c4s_odd", "c4s_m1"])
+@pytest.mark.parametrize("method", [0, 1])
+def test_fit_synthetic_matches_reference_golden(ctx, name, method):
+    g = load_golden(name)
+    seed, N, K, M, A = (int(v) for v in g["meta"])
+    ds = _capi.Dataset(ctx, synth=(seed, 0, N, K, M, 16))
+    pre = f"t{method + 1}_"
+    st = ds.fit(A, method)
+    assert_state_close(st, {k: g.get(pre + k) for k in "WPRQT"})
+    X, _ = ds.download()
+    assert np.array_equal(X[:4, :8], g["x_head"])
+    assert relerr(_capi.fitted(ctx, st["R"], st["Q"], A, np.eye(K)), g[pre + "coef_A"]) <= RTOL
+    assert relerr(_capi.fitted(ctx, st["R"], st["Q"], A, X[:64]), g[pre + "fitted_head"]) <= RTOL
+    ds.close()
+
+
+# every column-range of the pass-kernel dispatch, ragged N, M = 1 and M > 1
+SHAPES = [(3, 2, 1, 1), (40, 7, 1, 5), (33, 12, 2, 6), (257, 64, 3, 6), (200, 100, 5, 9), (64, 130, 8, 5),
+          (300, 255, 2, 7), (129, 401, 3, 8), (90, 513, 2, 6), (150, 1000, 4, 6), (70, 1500, 2, 5),
+          (64, 2048, 8, 6), (50, 2500, 3, 5), (40, 4096, 4, 6), (2000, 31, 9, 9)]
+
+
+@pytest.mark.parametrize("N,K,M,A", SHAPES)
+@pytest.mark.parametrize("method", [0, 1])
+def test_fit_matches_oracle(ctx, N, K, M, A, method):
+    X, Y = port.synth(1000 + N + K, N, K, M, L=max(A, 4))
+    want = port.fit(X, Y, A, method)
+    got = _capi.fit_host(ctx, X, Y, A, method)
+    assert_state_close(got, want, rtol=1e-8 if K > 1000 else RTOL)
+    Bw = port.coefficients(want["R"], want["Q"], A)
+    Bg = port.coefficients(got["R"], got["Q"], A)
+    assert relerr(Bg, Bw) <= RTOL
+
+
+def test_cross_products(ctx):
+    X, Y = port.synth(99, 3000, 300, 5)
+    ds = _capi.Dataset(ctx, X, Y)
+    assert relerr(ds.xty(), X.T @ Y) <= 1e-12
+    assert relerr(ds.xtx(), X.T @ X) <= 1e-12
+    ds.close()
+
+
+def test_type1_equals_type2_and_invariants(ctx):
+    ds = _capi.Dataset(ctx, synth=(7, 0, 5000, 384, 4, 16))
+    a = ds.fit(12, 0); b = ds.fit(12, 1)
+    assert_state_close(a, b, keys="WPRQ")
+    R, P, W, T = a["R"], a["P"], a["W"], a["T"]
+    assert np.allclose(np.linalg.norm(W, axis=0), 1.0, atol=1e-12)
+    RtP = R.T @ P                                    # unit upper triangular
+    assert np.allclose(np.tril(RtP, -1), 0, atol=1e-9) and np.allclose(np.diag(RtP), 1, atol=1e-9)
+    TtT = T.T @ T
+    off = TtT - np.diag(np.diag(TtT))
+    assert np.abs(off).max() <= 1e-9 * np.abs(np.diag(TtT)).max()
+    # run-to-run reproducibility (no atomics)
+    c = ds.fit(12, 0)
+    assert all(np.array_equal(a[k], c[k]) for k in "WPRQT")
+    ds.close()
+
+
+def test_predict_helpers_match_oracle(ctx):
+    X, Y = port.synth(31, 500, 90, 3)
+    st = port.fit(X, Y, 7, 0)
+    Xn, Yn = port.synth(32, 123, 90, 3)
+    R, Q = st["R"], st["Q"]
+    assert relerr(_capi.scores(ctx, R, 5, Xn), port.scores(R, 5, Xn)) <= RTOL
+    assert relerr(_capi.fitted(ctx, R, Q, 4, Xn), port.fitted_values(R, Q, 4, Xn)) <= RTOL
+    assert relerr(_capi.fitted(ctx, R, Q, 7, Xn, Yn), port.residuals(R, Q, 7, Xn, Yn)) <= RTOL
+    assert relerr(_capi.predict_residuals(ctx, R, Q, Xn, Yn), port.predict_residuals(R, Q, Xn, Yn)) <= RTOL
+    g = load_golden("c2_nir_octane")
+    ds = _capi.Dataset(ctx, g["X"], g["Y"])
+    s2 = ds.fit(10, 0)
+    nd = _capi.predict_residuals(ctx, s2["R"], s2["Q"], g["X"][:7], g["Y"][:7])
+    assert relerr(nd, g["new_data"]) <= RTOL
+    ds.close()
+
+
+def test_argument_errors(ctx):
+    X, Y = port.synth(1, 20, 5, 1)
+    ds = _capi.Dataset(ctx, X, Y)
+    with pytest.raises(_capi.PlsbError):
+        ds.fit(0, 0)
+    with pytest.raises(_capi.PlsbError):
+        ds.fit(2, 7)
+    ds.close()
