@@ -180,14 +180,14 @@ class Dataset:
         check(lib().plsb_xtx(self.h, P(G)))
         return G
 
-    def cv_folds(self, A, method, test_idx, nfolds_total=None, fold0=0, out=None):
-        """test_idx: (nfolds_local, test_size) int64 rows left out per fold.  Returns E[M][rows][A]."""
+    def cv_folds(self, A, method, test_idx, fold0=0, nfolds_local=None, out=None):
+        """test_idx: (nfolds_total, test_size) int64 rows left out per fold; folds [fold0, fold0+nfolds_local)
+        are computed by this call (fold sharding).  Returns E[M][nfolds_total*test_size][A]."""
         test_idx = np.ascontiguousarray(test_idx, dtype=np.int64)
-        nloc, ts = test_idx.shape
-        ntot = nloc if nfolds_total is None else nfolds_total
-        rows = ntot * ts
+        ntot, ts = test_idx.shape
+        nloc = ntot - fold0 if nfolds_local is None else nfolds_local
         if out is None:
-            out = np.zeros((self.M, A, rows))
+            out = np.zeros((self.M, A, ntot * ts))
         check(lib().plsb_cv_folds(self.h, i64(A), C.c_int(method), i64(ntot), i64(ts), IP(test_idx), i64(fold0),
                                   i64(nloc), P(out)))
         return out.transpose(0, 2, 1)

@@ -1,10 +1,174 @@
-// pls_b200/csrc/cv.cu — batched cross-validation (placeholder until the Gram-downdate engine lands)
+// pls_b200/csrc/cv.cu — batched cross-validation: many independent folds per launch.
+//
+// Replaces Model::cv_LOO (reference src/pls.cpp:469-491) and Model::cv_LSO (512-549): N resp.
+// num_trials refits, each followed by A residual evaluations of the held-out rows.
+//
+// The reference never re-centres folds (z-scoring happens once, in the CLI), so a fold's cross products
+// are low-rank downdates of the full ones:
+//      S_f = X'Y - X_H' Y_H ,      (X'X)_f r = (X'X) r - X_H' (X_H r)       H = held-out rows of fold f.
+// Per component the whole wave of F folds shares ONE FP64 DMMA GEMM  (X'X) [r_1 .. r_F]  (gemm.cu), and a
+// one-CTA-per-fold kernel does the K-sized algebra (downdate, tt, p, q, deflation of S_f, next w and r —
+// the same code as the single-fit step, step_core.cuh).  The scores of the held-out rows, u = X_H r_a,
+// fall out of the downdate, so the residuals for every prefix 1..A are a running update
+// e_a = e_{a-1} - u q_a' : no separate prediction pass.
+// Components are extracted up to A only (the reference extracts K per fold, pls.cpp:477/531; its first A
+// are bit-identical).
+#include <vector>
+
 #include "internal.h"
+#include "step_core.cuh"
+
+namespace plsb {
+
+constexpr int CV_NT = 256;
+
+struct CvArgs {
+    const double *X, *Y, *S0;
+    const int64_t *test_idx;   // device, [local folds][ts]
+    double *S, *P, *R, *w, *Gr, *U, *E;
+    int64_t rows_local;        // columns of E hold rows_local entries
+    int K, ldk, ldm, M, A, ts;
+    int f0;                    // first local fold of this wave
+    int a;                     // component whose GEMM just finished (-1: initialise)
+};
+
+__global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
+    __shared__ StepSmem<CV_NT> sh;
+    __shared__ double qdump[PLSB_MAX_M];
+    const int tid = threadIdx.x;
+    const int f = blockIdx.x;
+    const int64_t gf = (int64_t)v.f0 + f;
+    const int64_t *h = v.test_idx + gf * v.ts;
+    const int K = v.K, ldk = v.ldk, M = v.M;
+    double *Sf = v.S + (size_t)f * M * ldk;
+    double *Pf = v.P + (size_t)f * v.A * ldk;
+    double *Rf = v.R + (size_t)f * v.A * ldk;
+
+    if (v.a < 0) {
+        // S_f = S0 - X_H' Y_H
+        for (int k = tid; k < ldk; k += CV_NT)
+            for (int m = 0; m < M; ++m) {
+                double s = v.S0[(size_t)m * ldk + k];
+                if (k < K)
+                    for (int i = 0; i < v.ts; ++i) s -= v.X[h[i] * (int64_t)ldk + k] * v.Y[h[i] * (int64_t)v.ldm + m];
+                Sf[(size_t)m * ldk + k] = s;
+            }
+        __syncthreads();
+    } else {
+        const double *r = Rf + (size_t)v.a * ldk;
+        double *g = v.Gr + (size_t)f * ldk;
+        double *U = v.U + (size_t)f * v.ts;
+        // downdate: g = (X'X) r - X_H' (X_H r); u = X_H r are the held-out scores of this component
+        for (int i0 = 0; i0 < v.ts; i0 += 256) {
+            const int ni = v.ts - i0 < 256 ? v.ts - i0 : 256;
+            warp_dots<CV_NT>(ni, K, [&](int i) { return v.X + h[i0 + i] * (int64_t)ldk; }, [&](int) { return r; }, sh.c);
+            __syncthreads();
+            for (int k = tid; k < K; k += CV_NT) {
+                double acc = g[k];
+                for (int i = 0; i < ni; ++i) acc -= sh.c[i] * v.X[h[i0 + i] * (int64_t)ldk + k];
+                g[k] = acc;
+            }
+            for (int i = tid; i < ni; i += CV_NT) U[i0 + i] = sh.c[i];
+            __syncthreads();
+        }
+        double acc = 0.0;
+        for (int k = tid; k < K; k += CV_NT) acc = fma(r[k], g[k], acc);
+        const double tt = block_sum<CV_NT>(acc, sh);
+        finish_component<CV_NT>(K, ldk, M, Sf, g, tt, r, Pf + (size_t)v.a * ldk, qdump, sh);
+        // residuals of the held-out rows with a+1 components: e_a = e_{a-1} - u q_a'
+        for (int e = tid; e < v.ts * M; e += CV_NT) {
+            const int i = e / M, m = e % M;
+            const int64_t row = gf * v.ts + i;
+            const double prev = (v.a == 0) ? v.Y[h[i] * (int64_t)v.ldm + m]
+                                           : v.E[((size_t)m * v.A + (v.a - 1)) * v.rows_local + row];
+            v.E[((size_t)m * v.A + v.a) * v.rows_local + row] = prev - U[i] * sh.q[m];
+        }
+        __syncthreads();
+    }
+    const int an = v.a + 1;
+    if (an >= v.A) return;
+    next_weights<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, sh);
+}
+
+struct CvBuf {
+    void *p = nullptr;
+    ~CvBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) { PLSB_CUDA(cudaMalloc(&p, bytes ? bytes : 8)); return PLSB_OK; }
+    double *d() { return (double *)p; }
+};
+
+}  // namespace plsb
+
 using namespace plsb;
+
 extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
                              const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E) {
-    (void)ds; (void)A; (void)method; (void)nfolds_total; (void)test_size; (void)test_idx; (void)fold0;
-    (void)nfolds_local; (void)E;
-    set_error("plsb_cv_folds: not implemented yet");
-    return PLSB_ERR_UNSUPPORTED;
+    PLSB_ARG(ds && test_idx && E, "null argument");
+    PLSB_ARG(A >= 1, "A must be >= 1");
+    PLSB_ARG(method == PLSB_KERNEL_TYPE1 || method == PLSB_KERNEL_TYPE2, "unknown method %d", method);
+    PLSB_ARG(test_size >= 1 && test_size < ds->N, "test_size %lld must be in [1, N)", (long long)test_size);
+    PLSB_ARG(fold0 >= 0 && nfolds_local >= 0 && fold0 + nfolds_local <= nfolds_total, "bad fold range");
+    PLSB_ARG(ds->M <= PLSB_MAX_M, "M=%lld exceeds the in-kernel eigen solver limit (%d)", (long long)ds->M, PLSB_MAX_M);
+    PLSB_ARG(!ds->sharded, "cross-validation wants the full data set on every GPU (folds are sharded, not rows)");
+    if (nfolds_local == 0) return PLSB_OK;
+    plsb_ctx *c = ds->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    const int64_t K = ds->K, ldk = ds->ldk, M = ds->M, ts = test_size;
+    const int64_t *tloc = test_idx + fold0 * ts;
+    for (int64_t i = 0; i < nfolds_local * ts; ++i)
+        PLSB_ARG(tloc[i] >= 0 && tloc[i] < ds->N, "test index %lld out of range", (long long)tloc[i]);
+    const int64_t rows_local = nfolds_local * ts, rows_total = nfolds_total * ts;
+
+    CvBuf G, S0, idx, Ed, S, P, R, w, Gr, U;
+    const int64_t ldg = round_up(K, 2);
+    PLSB_TRY(G.alloc((size_t)K * ldg * 8));
+    PLSB_CUDA(cudaMemsetAsync(G.p, 0, (size_t)K * ldg * 8, c->stream));
+    PLSB_TRY(S0.alloc((size_t)M * ldk * 8));
+    PLSB_TRY(launch_xtx(c, ds, G.d(), ldg));
+    PLSB_TRY(launch_xty_pass(c, ds, S0.d()));
+    PLSB_TRY(idx.alloc((size_t)rows_local * sizeof(int64_t)));
+    PLSB_CUDA(cudaMemcpyAsync(idx.p, tloc, (size_t)rows_local * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+    PLSB_TRY(Ed.alloc((size_t)M * A * rows_local * 8));
+
+    // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles
+    size_t free_b = 0, total_b = 0;
+    PLSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    const size_t per_fold = (size_t)(M + 2 * A + 2) * ldk * 8 + (size_t)ts * 8;
+    int64_t F = (int64_t)((double)free_b * 0.6 / (double)per_fold);
+    if (F > 4096) F = 4096;
+    if (const char *e = getenv("PLSB_FOLD_BATCH")) { const int64_t v = atoll(e); if (v > 0 && v < F) F = v; }
+    if (F > nfolds_local) F = nfolds_local;
+    PLSB_ARG(F >= 1, "not enough device memory for one fold");
+    PLSB_TRY(S.alloc((size_t)F * M * ldk * 8));
+    PLSB_TRY(P.alloc((size_t)F * A * ldk * 8));
+    PLSB_TRY(R.alloc((size_t)F * A * ldk * 8));
+    PLSB_TRY(w.alloc((size_t)F * ldk * 8));
+    PLSB_TRY(Gr.alloc((size_t)F * ldk * 8));
+    PLSB_TRY(U.alloc((size_t)F * ts * 8));
+
+    CvArgs v{};
+    v.X = ds->X; v.Y = ds->Y; v.S0 = S0.d(); v.test_idx = (const int64_t *)idx.p;
+    v.S = S.d(); v.P = P.d(); v.R = R.d(); v.w = w.d(); v.Gr = Gr.d(); v.U = U.d(); v.E = Ed.d();
+    v.rows_local = rows_local; v.K = (int)K; v.ldk = (int)ldk; v.ldm = (int)ds->ldm; v.M = (int)M; v.A = (int)A;
+    v.ts = (int)ts;
+    for (int64_t f0 = 0; f0 < nfolds_local; f0 += F) {
+        const int nf = (int)(nfolds_local - f0 < F ? nfolds_local - f0 : F);
+        v.f0 = (int)f0;
+        for (int a = -1; a < (int)A; ++a) {
+            v.a = a;
+            if (a >= 0)  // Gr[f][:] = (X'X) r_f for the whole wave: one DMMA GEMM
+                PLSB_TRY(launch_gemm_atb(c, G.d(), ldg, R.d() + (size_t)a * ldk, A * ldk, K, (int)K, nf, Gr.d(), ldk,
+                                         false, true, true, PLSB_PROF_CV_GEMM));
+            {
+                ProfScope ps(c, PLSB_PROF_CV_FOLD);
+                cv_fold_kernel<<<nf, CV_NT, 0, c->stream>>>(v);
+            }
+            c->launches++;
+            PLSB_CUDA(cudaGetLastError());
+        }
+    }
+    PLSB_CUDA(cudaMemcpy2DAsync(E + fold0 * ts, (size_t)rows_total * 8, Ed.p, (size_t)rows_local * 8,
+                                (size_t)rows_local * 8, (size_t)(M * A), cudaMemcpyDeviceToHost, c->stream));
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
 }

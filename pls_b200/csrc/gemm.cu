@@ -14,6 +14,8 @@
 namespace plsb {
 
 constexpr int GM_BM = 128, GM_BN = 128, GM_BK = 16, GM_LD = 132, GM_NT = 256, GM_STAGES = 3;
+constexpr int GM_LDBN = GM_BK + 4;                       // n-major B tile: [BN][BK + 4]
+constexpr int GM_BS_KMAJOR = GM_BK * GM_LD, GM_BS_NMAJOR = GM_BN * GM_LDBN;
 
 struct GemmArgs {
     const double *A; int64_t lda;   // Kd x M
@@ -23,6 +25,8 @@ struct GemmArgs {
     int64_t k_per_split;            // multiple of GM_BK
     double *part;                   // [splitk][ntiles][BM*BN]
     int syrk;
+    int transC;                     // write C[n*ldc + m] instead of C[m*ldc + n]
+    double *C; int64_t ldc;         // direct output when splitk == 1
 };
 
 __device__ __forceinline__ void cp_async16(void *dst, const void *src, bool pred) {
@@ -46,10 +50,14 @@ __device__ __forceinline__ void syrk_tile(int t, int T, int &tm, int &tn) {
     tm = row; tn = row + t;
 }
 
+// B_NMAJOR: B is given as N x Kd (each column of the product contiguous along the reduction axis), the
+// layout of a batch of per-fold vectors.
+template <bool B_NMAJOR>
 __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
     extern __shared__ __align__(128) char smem[];
     double *As = reinterpret_cast<double *>(smem);                       // [STAGES][BK][LD]
     double *Bs = As + (size_t)GM_STAGES * GM_BK * GM_LD;
+    constexpr int BS_STAGE = B_NMAJOR ? GM_BS_NMAJOR : GM_BS_KMAJOR;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = blockIdx.x % g.ntiles, split = blockIdx.x / g.ntiles;
     int tm, tn;
@@ -69,9 +77,17 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
             const int kr = ch / (GM_BM / 2), cc = (ch % (GM_BM / 2)) * 2;
             const int64_t k = k0 + kr;
             const bool kin = k < k_end;
-            const bool pa = kin && (m_base + cc) < g.M, pb = kin && (n_base + cc) < g.N;
+            const bool pa = kin && (m_base + cc) < g.M;
             cp_async16(As + ((size_t)st * GM_BK + kr) * GM_LD + cc, pa ? g.A + k * g.lda + m_base + cc : g.A, pa);
-            cp_async16(Bs + ((size_t)st * GM_BK + kr) * GM_LD + cc, pb ? g.B + k * g.ldb + n_base + cc : g.B, pb);
+            if (!B_NMAJOR) {
+                const bool pb = kin && (n_base + cc) < g.N;
+                cp_async16(Bs + (size_t)st * BS_STAGE + kr * GM_LD + cc, pb ? g.B + k * g.ldb + n_base + cc : g.B, pb);
+            } else {
+                const int n = ch / (GM_BK / 2), kc = (ch % (GM_BK / 2)) * 2;
+                const bool pb = (k0 + kc) < k_end && (n_base + n) < g.N;
+                cp_async16(Bs + (size_t)st * BS_STAGE + n * GM_LDBN + kc,
+                           pb ? g.B + (int64_t)(n_base + n) * g.ldb + k0 + kc : g.B, pb);
+            }
         }
     };
 
@@ -96,14 +112,15 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
             cp_async_commit();
         }
         const double *as = As + (size_t)(kt % GM_STAGES) * GM_BK * GM_LD;
-        const double *bs = Bs + (size_t)(kt % GM_STAGES) * GM_BK * GM_LD;
+        const double *bs = Bs + (size_t)(kt % GM_STAGES) * BS_STAGE;
 #pragma unroll
         for (int kk = 0; kk < GM_BK / 4; ++kk) {
             double a[8], b[4];
 #pragma unroll
             for (int i = 0; i < 8; ++i) a[i] = as[(kk * 4 + fk) * GM_LD + wm + i * 8 + fr];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) b[j] = bs[(kk * 4 + fk) * GM_LD + wn + j * 8 + fr];
+            for (int j = 0; j < 4; ++j)
+                b[j] = B_NMAJOR ? bs[(wn + j * 8 + fr) * GM_LDBN + kk * 4 + fk] : bs[(kk * 4 + fk) * GM_LD + wn + j * 8 + fr];
 #pragma unroll
             for (int i = 0; i < 8; ++i)
 #pragma unroll
@@ -111,6 +128,23 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
         }
     }
     cp_async_wait<0>();
+    if (g.splitk == 1 && !g.syrk) {  // no partials needed: write the product directly
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int m = m_base + wm + i * 8 + fr, n = n_base + wn + j * 8 + fk * 2;
+                if (m >= g.M) continue;
+                if (!g.transC) {
+                    if (n < g.N) g.C[(int64_t)m * g.ldc + n] = acc[i][j][0];
+                    if (n + 1 < g.N) g.C[(int64_t)m * g.ldc + n + 1] = acc[i][j][1];
+                } else {
+                    if (n < g.N) g.C[(int64_t)n * g.ldc + m] = acc[i][j][0];
+                    if (n + 1 < g.N) g.C[(int64_t)(n + 1) * g.ldc + m] = acc[i][j][1];
+                }
+            }
+        return;
+    }
     double *out = g.part + ((size_t)split * g.ntiles + tile) * (GM_BM * GM_BN);
 #pragma unroll
     for (int i = 0; i < 8; ++i)
@@ -133,18 +167,21 @@ __global__ void __launch_bounds__(256) gemm_reduce_kernel(const GemmArgs g, doub
         if (m >= g.M || n >= g.N) continue;
         double s = 0.0;
         for (int sp = 0; sp < g.splitk; ++sp) s += g.part[((size_t)sp * g.ntiles + tile) * (GM_BM * GM_BN) + e];
-        C[(int64_t)m * ldc + n] = s;
+        if (g.transC) C[(int64_t)n * ldc + m] = s;
+        else C[(int64_t)m * ldc + n] = s;
         if (g.syrk && tm != tn) C[(int64_t)n * ldc + m] = s;
     }
 }
 
-// C (M x N, row-major, ldc) = A' B.  syrk: A == B, M == N, C symmetric.
+// C (M x N, row-major, ldc) = A' B.  syrk: A == B, M == N, C symmetric.  b_nmajor: B given as N x Kd.
+// transC: store C transposed (N x M, row-major).
 int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
-                    double *C, int64_t ldc, bool syrk, int prof_slot) {
+                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot) {
     if (M == 0 || N == 0) return PLSB_OK;
     PLSB_ARG((lda % 2) == 0 && (ldb % 2) == 0, "gemm: leading dimensions must be even");
     GemmArgs g{};
     g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.Kd = Kd; g.M = M; g.N = N; g.syrk = syrk ? 1 : 0;
+    g.transC = transC ? 1 : 0; g.C = C; g.ldc = ldc;
     g.tiles_m = (int)ceil_div(M, GM_BM);
     g.tiles_n = (int)ceil_div(N, GM_BN);
     g.ntiles = syrk ? g.tiles_m * (g.tiles_m + 1) / 2 : g.tiles_m * g.tiles_n;
@@ -155,19 +192,26 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
     if (want < 1) want = 1;
     g.k_per_split = round_up(ceil_div(Kd > 0 ? Kd : 1, want), GM_BK);
     g.splitk = (int)ceil_div(Kd > 0 ? Kd : 1, g.k_per_split);
-    const size_t pbytes = (size_t)g.splitk * g.ntiles * GM_BM * GM_BN * sizeof(double);
-    PLSB_TRY(ensure_part(c, pbytes));
-    g.part = c->part;
-    const size_t smem = (size_t)2 * GM_STAGES * GM_BK * GM_LD * sizeof(double);
-    PLSB_CUDA(cudaFuncSetAttribute(dmma_atb_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const bool direct = g.splitk == 1 && !syrk;
+    if (!direct) {
+        const size_t pbytes = (size_t)g.splitk * g.ntiles * GM_BM * GM_BN * sizeof(double);
+        PLSB_TRY(ensure_part(c, pbytes));
+        g.part = c->part;
+    }
+    const size_t smem = (size_t)GM_STAGES * (GM_BK * GM_LD + (b_nmajor ? GM_BS_NMAJOR : GM_BS_KMAJOR)) * sizeof(double);
+    auto kern = b_nmajor ? dmma_atb_kernel<true> : dmma_atb_kernel<false>;
+    PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope ps(c, prof_slot);
-        dmma_atb_kernel<<<(unsigned)(g.ntiles * g.splitk), GM_NT, smem, c->stream>>>(g);
+        kern<<<(unsigned)(g.ntiles * g.splitk), GM_NT, smem, c->stream>>>(g);
     }
     PLSB_CUDA(cudaGetLastError());
-    gemm_reduce_kernel<<<(unsigned)g.ntiles, 256, 0, c->stream>>>(g, C, ldc);
-    PLSB_CUDA(cudaGetLastError());
-    c->launches += 2;
+    c->launches += 1;
+    if (!direct) {
+        gemm_reduce_kernel<<<(unsigned)g.ntiles, 256, 0, c->stream>>>(g, C, ldc);
+        PLSB_CUDA(cudaGetLastError());
+        c->launches += 1;
+    }
     return PLSB_OK;
 }
 
@@ -177,7 +221,7 @@ int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg) {
         return PLSB_OK;
     }
     return launch_gemm_atb(c, ds->X, ds->ldk, ds->X, ds->ldk, ds->N, (int)ds->K, (int)ds->K, G, ldg, true,
-                           PLSB_PROF_XTX);
+                           false, false, PLSB_PROF_XTX);
 }
 
 }  // namespace plsb

@@ -80,6 +80,11 @@ int launch_step(plsb_ctx *c, const StepArgs &s);
 // y = G r, tt = r'G r for symmetric G (K x K, ld = ldg): KERNEL_TYPE2 per-component product
 int launch_symv(plsb_ctx *c, const double *G, int64_t ldg, int K, const double *r, double *out /*ldk+1*/, int ldk);
 
+// ---- FP64 DMMA contraction (gemm.cu) --------------------------------------------------------------
+int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
+                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot);
+int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg);
+
 // ---- synthetic data (synth.cu) ----------------------------------------------------------------
 int launch_synth(plsb_ctx *c, uint64_t seed, int64_t row0, int64_t N, int64_t K, int64_t M, int64_t L,
                  double *X, int64_t ldk, double *Y, int64_t ldm);

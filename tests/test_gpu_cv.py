@@ -1,0 +1,122 @@
+"""Parity of the batched cross-validation engine (plsb_cv_folds, Gram-downdate + DMMA GEMM) with the
+reference's cv_LOO / cv_LSO residuals (golden vectors from the unmodified reference) and with the CPU
+oracle's explicit per-fold refits.  optimal_num_components must match exactly."""
+import numpy as np
+import pytest
+
+from oracle import port
+from pls_b200 import _capi
+from pls_b200.model import MSE, RESS, Model, optimal_num_components, validation
+from tests.util import RTOL, load_golden, relerr
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = _capi.Context(0)
+    yield c
+    c.close()
+
+
+def loo_idx(N):
+    return np.arange(N, dtype=np.int64).reshape(-1, 1)
+
+
+def test_c1_toy_loo_lso(ctx):
+    g = load_golden("c1_toy")
+    ds = _capi.Dataset(ctx, g["X"], g["Y"])
+    loo = ds.cv_folds(2, 0, loo_idx(10))
+    assert relerr(loo, g["loo"]) <= RTOL
+    lso = ds.cv_folds(2, 0, g["lso_test"].astype(np.int64))
+    assert relerr(lso, g["lso"]) <= RTOL
+    assert relerr(_capi.validation(loo, 0), g["loo_ress"]) <= RTOL
+    assert relerr(_capi.validation(lso, 1), g["lso_mse"]) <= RTOL
+    assert np.array_equal(_capi.optimal_num_components(loo), g["loo_opt"])
+    assert np.array_equal(_capi.optimal_num_components(lso), g["lso_opt"])
+    ds.close()
+
+
+@pytest.mark.parametrize("method", [0, 1])
+def test_c2_nir_octane_loo(ctx, method):
+    g = load_golden("c2_nir_octane")
+    ds = _capi.Dataset(ctx, g["X"], g["Y"])
+    loo = ds.cv_folds(10, method, loo_idx(60))
+    assert relerr(loo, g["loo" if method == 0 else "loo_t2"]) <= RTOL
+    assert relerr(_capi.validation(loo, 1), g["loo_mse"]) <= RTOL          # RMSEP within 1e-9
+    assert np.array_equal(_capi.optimal_num_components(loo), g["loo_opt"])  # exactly (= 3)
+    te = g["lso_test"].astype(np.int64)
+    lso = ds.cv_folds(10, method, te)
+    assert relerr(lso[:, :20 * 18, :], g["lso_first"]) <= RTOL
+    assert relerr(_capi.validation(lso, 0), g["lso_ress"]) <= RTOL
+    assert np.array_equal(_capi.optimal_num_components(lso), g["lso_opt"])
+    ds.close()
+
+
+def test_c3_nir_pls2_lso_1000_folds(ctx):
+    g = load_golden("c3_nir_pls2")
+    ds = _capi.Dataset(ctx, g["X"], g["Y"])
+    te = g["lso_test"].astype(np.int64)
+    lso = ds.cv_folds(10, 0, te)
+    assert relerr(lso[:, :50 * 18, :], g["lso_first"]) <= RTOL
+    assert relerr(lso[:, -18:, :], g["lso_last"]) <= RTOL
+    assert relerr(_capi.validation(lso, 0), g["lso_ress"]) <= RTOL
+    assert relerr(_capi.validation(lso, 1), g["lso_mse"]) <= RTOL
+    assert np.array_equal(_capi.optimal_num_components(lso), g["lso_opt"])
+    ds.close()
+
+
+def test_c5s_loo(ctx):
+    g = load_golden("c5s_loo")
+    seed, N, K, M, A = (int(v) for v in g["meta"])
+    ds = _capi.Dataset(ctx, synth=(seed, 0, N, K, M, 16))
+    loo = ds.cv_folds(A, 0, loo_idx(N))
+    assert relerr(loo, g["loo"]) <= RTOL
+    assert relerr(_capi.validation(loo, 0), g["loo_ress"]) <= RTOL
+    assert np.array_equal(_capi.optimal_num_components(loo), g["loo_opt"])
+    ds.close()
+
+
+@pytest.mark.parametrize("N,K,M,A,ts,nf", [(45, 11, 2, 5, 9, 30), (200, 77, 1, 6, 1, 200), (120, 300, 3, 5, 40, 7),
+                                           (64, 130, 8, 4, 3, 50), (700, 20, 2, 4, 300, 3)])
+def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
+    X, Y = port.synth(500 + N + K, N, K, M, L=max(A, 4))
+    rng = np.random.default_rng(N)
+    te = np.stack([rng.permutation(N)[:ts] for _ in range(nf)]).astype(np.int64) if ts > 1 else loo_idx(N)[:nf]
+    want = port.cv_folds(X, Y, A, 0, te)
+    ds = _capi.Dataset(ctx, X, Y)
+    got = ds.cv_folds(A, 0, te)
+    assert relerr(got, want) <= RTOL
+    # fold sharding: two calls covering disjoint fold ranges fill the same residual block
+    out = np.zeros((M, A, nf * ts))
+    h = nf // 2
+    ds.cv_folds(A, 0, te, fold0=0, nfolds_local=h, out=out)
+    ds.cv_folds(A, 0, te, fold0=h, nfolds_local=nf - h, out=out)
+    assert np.array_equal(out.transpose(0, 2, 1), got)
+    # small waves give the same answer as one big wave
+    import os
+    os.environ["PLSB_FOLD_BATCH"] = "3"
+    try:
+        assert np.array_equal(ds.cv_folds(A, 0, te), got)
+    finally:
+        del os.environ["PLSB_FOLD_BATCH"]
+    ds.close()
+
+
+def test_model_mirror_reads_like_the_reference(ctx):
+    g = load_golden("c2_nir_octane")
+    m = Model(g["X"], g["Y"], 0, 10, ctx=ctx)
+    assert relerr(m.coefficients(), g["coef_A"]) <= RTOL
+    assert relerr(m.fitted_values(g["X"]), g["fitted_A"]) <= RTOL
+    assert relerr(np.array([m.SSE(g["X"], g["Y"], c) for c in range(1, 11)]), g["sse"]) <= 1e-8
+    assert np.abs(np.array([m.explained_variance(g["X"], g["Y"], c) for c in range(1, 11)]) - g["ev"]).max() <= 1e-9
+    loo = m.cv_LOO()
+    assert loo.method() == "LOO" and len(loo.errors()) == 1 and loo.errors()[0].shape == (60, 10)
+    assert relerr(validation(loo, MSE), g["loo_mse"]) <= RTOL
+    assert list(optimal_num_components(loo)) == [3]
+    lso = m.cv_LSO(0.3, 600)
+    assert relerr(validation(lso, RESS), g["lso_ress"]) <= RTOL
+    assert np.array_equal(optimal_num_components(lso), g["lso_opt"])
+    nd = m.cv_NEW_DATA(g["X"][:7], g["Y"][:7])
+    assert nd.method() == "NEW DATA" and relerr(nd.array, g["new_data"]) <= RTOL
+    assert m.loadingsX(3).shape == (401, 3) and m.loadingsY().shape == (1, 10)
