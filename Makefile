@@ -25,17 +25,19 @@ build/%.o: $(CSRC)/%.cu $(HDR)
 	@mkdir -p build
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 
+HOSTSRC := pls_b200/host/model.cpp pls_b200/host/stats.cpp pls_b200/host/engine.cpp
 ifneq ($(EIGEN_INC),)
-ifneq ($(wildcard pls_b200/host/model.cpp),)
-HOSTFLAGS := -std=c++17 -O2 -fPIC -Iinclude -I$(EIGEN_INC)
-host: pls_b200/libpls.so pls_b200/PLS
-pls_b200/libpls.so: pls_b200/host/model.cpp pls_b200/host/stats.cpp include/PLS/pls.h $(LIB)
-	$(CXX) $(HOSTFLAGS) -shared -o $@ pls_b200/host/model.cpp pls_b200/host/stats.cpp -Lpls_b200 -lplsb -Wl,-rpath,'$$ORIGIN'
+# The C++ drop-in layer needs Eigen headers (the reference's own public dependency).  They are not in this
+# repo: EIGEN_INC points at a system Eigen or at the reference checkout's submodule.  On a box without
+# Eigen the prebuilt libpls.so / PLS / api_check (shipped with the snapshot) are used as they are.
+HOSTFLAGS := -std=c++17 -O2 -fPIC -Wall -Iinclude -I$(EIGEN_INC)
+host: pls_b200/libpls.so pls_b200/PLS tests/cpp/api_check
+pls_b200/libpls.so: $(HOSTSRC) pls_b200/host/engine.h include/PLS/pls.h include/plsb.h $(LIB)
+	$(CXX) $(HOSTFLAGS) -shared -o $@ $(HOSTSRC) -Lpls_b200 -lplsb -lpthread -Wl,-rpath,'$$ORIGIN'
 pls_b200/PLS: pls_b200/host/main.cpp pls_b200/libpls.so
-	$(CXX) $(HOSTFLAGS) -o $@ pls_b200/host/main.cpp -Lpls_b200 -lpls -lplsb -Wl,-rpath,'$$ORIGIN'
-else
-host:
-endif
+	$(CXX) $(HOSTFLAGS) -o $@ pls_b200/host/main.cpp -Lpls_b200 -lpls -lplsb -lpthread -Wl,-rpath,'$$ORIGIN'
+tests/cpp/api_check: tests/cpp/api_check.cpp pls_b200/libpls.so
+	$(CXX) $(HOSTFLAGS) -o $@ tests/cpp/api_check.cpp -Lpls_b200 -lpls -lplsb -lpthread -Wl,-rpath,'$$ORIGIN/../../pls_b200'
 else
 host:
 	@echo "host: no Eigen headers found (set EIGEN_INC); using prebuilt libpls.so / PLS if present"
@@ -45,5 +47,5 @@ oracle:
 	$(MAKE) -C oracle
 
 clean:
-	rm -rf build $(LIB) pls_b200/libpls.so pls_b200/PLS
+	rm -rf build $(LIB) pls_b200/libpls.so pls_b200/PLS tests/cpp/api_check
 .PHONY: all host oracle clean

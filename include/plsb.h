@@ -96,6 +96,19 @@ int plsb_predict_residuals(plsb_ctx_t ctx, const double *R, const double *Q, int
                            int64_t A, const double *Xn, int64_t ldx, int64_t Nn, const double *Yn,
                            int64_t ldy, double *E);
 
+/* B = R[:, :comp] * Q[:, :comp]'   (K x M col-major; pls.cpp:444-447) */
+int plsb_coefficients(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_t M, int64_t comp,
+                      double *B);
+/* sse[(c-1)*M + m] = sum_i (Yn - Xn B_c)[i, m]^2 for every c = 1..A in ONE pass over Xn (M x A col-major):
+ * Model::SSE (pls.cpp:457-459) for all component counts, what print_explained_variance (pls.cpp:551-562)
+ * and explained_variance (461-467) consume. */
+int plsb_sse_prefixes(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_t M, int64_t A,
+                      const double *Xn, int64_t ldx, int64_t Nn, const double *Yn, int64_t ldy, double *sse);
+
+/* sse[m] for one component count (Model::SSE, pls.cpp:457-459) */
+int plsb_sse(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_t M, int64_t comp, const double *Xn,
+             int64_t ldx, int64_t Nn, const double *Yn, int64_t ldy, double *sse);
+
 /* ---- cross-validation: cv_LOO (pls.cpp:469-491), cv_LSO (pls.cpp:512-549) ------------------- */
 /* nfolds folds, each leaving out test_size rows: test_idx[f*test_size + i].  The training set of a
  * fold is the complement (cross products are order-independent up to rounding, so the reference's

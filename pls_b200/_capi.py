@@ -23,7 +23,8 @@ SYMBOLS = [
     "plsb_dataset_create", "plsb_dataset_create_device", "plsb_dataset_create_synth", "plsb_dataset_destroy",
     "plsb_dataset_shape", "plsb_dataset_download", "plsb_dataset_set_sharded",
     "plsb_fit", "plsb_fit_host", "plsb_xty", "plsb_xtx",
-    "plsb_scores", "plsb_fitted", "plsb_predict_residuals", "plsb_cv_folds",
+    "plsb_scores", "plsb_fitted", "plsb_predict_residuals", "plsb_coefficients", "plsb_sse_prefixes", "plsb_sse",
+    "plsb_cv_folds",
     "plsb_normalcdf", "plsb_wilcoxon", "plsb_validation", "plsb_optimal_num_components", "plsb_lso_folds",
     "plsb_profile_enable", "plsb_profile_reset", "plsb_profile_get", "plsb_launch_count",
 ]

@@ -4,6 +4,8 @@
 // 449-451 + residuals 453-455, and cv_NEW_DATA 494-510.  The reference rebuilds R_c Q_c' and re-reads
 // X_new for every component count; here ONE pass over X_new yields the scores S = X_new R for all A
 // components and the residuals for every prefix c follow from a running sum of s_a q_a'.
+#include <vector>
+
 #include "internal.h"
 
 namespace plsb {
@@ -70,6 +72,37 @@ __global__ void __launch_bounds__(256) prefix_residual_kernel(const double *__re
     if (mode == 2) out[(size_t)m * Nn + i] = y - acc;
 }
 
+// B[m*K + k] = sum_{a<comp} R[a*K + k] * Q[a*M + m]   (K x M column-major; pls.cpp:444-447)
+__global__ void __launch_bounds__(256) coefficients_kernel(const double *__restrict__ R, const double *__restrict__ Q,
+                                                           int K, int M, int comp, double *__restrict__ B) {
+    const int k = blockIdx.x * 256 + threadIdx.x, m = blockIdx.y;
+    if (k >= K) return;
+    double acc = 0.0;
+    for (int a = 0; a < comp; ++a) acc = fma(R[(size_t)a * K + k], Q[(size_t)a * M + m], acc);
+    B[(size_t)m * K + k] = acc;
+}
+
+// out[col] = sum_i E[col*Nn + i]^2, one CTA per column, fixed summation tree (pls.cpp:457-459, 251)
+__global__ void __launch_bounds__(256) colsumsq_kernel(const double *__restrict__ E, int64_t Nn, double *__restrict__ out) {
+    __shared__ double red[8];
+    const double *e = E + (size_t)blockIdx.x * Nn;
+    double s0 = 0.0, s1 = 0.0;
+    int64_t i = threadIdx.x;
+    for (; i + 256 < Nn; i += 512) {
+        s0 = fma(e[i], e[i], s0);
+        s1 = fma(e[i + 256], e[i + 256], s1);
+    }
+    for (; i < Nn; i += 256) s0 = fma(e[i], e[i], s0);
+    const double w = warp_sum(s0 + s1);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = w;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int j = 0; j < 8; ++j) t += red[j];
+        out[blockIdx.x] = t;
+    }
+}
+
 struct Tmp {
     double *p = nullptr;
     ~Tmp() { if (p) cudaFree(p); }
@@ -101,12 +134,15 @@ static int scores_device(plsb_ctx *c, const double *R, int64_t K, int64_t comp, 
 
 static int predict_common(plsb_ctx *c, const double *R, const double *Q, int64_t K, int64_t M, int64_t A, int64_t comp,
                           const double *Xn, int64_t ldx, int64_t Nn, const double *Yn, int64_t ldy, int mode,
-                          double *out) {
+                          double *out, bool want_sse = false) {
     PLSB_ARG(c && R && Q && out && (Nn == 0 || Xn), "null argument");
     PLSB_ARG(comp >= 1 && comp <= A, "component count %lld out of range", (long long)comp);
     PLSB_ARG(mode == 1 || Nn == 0 || Yn, "Y is null");
     PLSB_CUDA(cudaSetDevice(c->device));
-    if (Nn == 0) return PLSB_OK;
+    if (Nn == 0) {
+        if (want_sse) for (int64_t i = 0; i < M * (mode == 0 ? A : 1); ++i) out[i] = 0.0;
+        return PLSB_OK;
+    }
     Tmp Xd, Rd, Sd, Qd, Yd, Od;
     PLSB_TRY(scores_device(c, R, K, comp, Xn, ldx, Nn, Xd, Rd, Sd));
     const int64_t ldm = round_up(M, 2);
@@ -123,6 +159,20 @@ static int predict_common(plsb_ctx *c, const double *R, const double *Q, int64_t
                                                         Od.p);
     c->launches++;
     PLSB_CUDA(cudaGetLastError());
+    if (want_sse) {  // column sums of squares of the residual block: (m, c) -> out[c*M + m]
+        const int64_t nc = (mode == 0) ? A : 1;  // component counts per response in the block
+        Tmp Sd2;
+        PLSB_TRY(Sd2.alloc((size_t)M * nc));
+        colsumsq_kernel<<<(unsigned)(M * nc), 256, 0, c->stream>>>(Od.p, Nn, Sd2.p);
+        c->launches++;
+        PLSB_CUDA(cudaGetLastError());
+        std::vector<double> tmp((size_t)M * nc);
+        PLSB_CUDA(cudaMemcpyAsync(tmp.data(), Sd2.p, (size_t)M * nc * 8, cudaMemcpyDeviceToHost, c->stream));
+        PLSB_CUDA(cudaStreamSynchronize(c->stream));
+        for (int64_t m = 0; m < M; ++m)
+            for (int64_t a = 0; a < nc; ++a) out[a * M + m] = tmp[(size_t)(m * nc + a)];
+        return PLSB_OK;
+    }
     PLSB_CUDA(cudaMemcpyAsync(out, Od.p, on * 8, cudaMemcpyDeviceToHost, c->stream));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
     return PLSB_OK;
@@ -155,6 +205,36 @@ int plsb_fitted(plsb_ctx_t c, const double *R, const double *Q, int64_t K, int64
 int plsb_predict_residuals(plsb_ctx_t c, const double *R, const double *Q, int64_t K, int64_t M, int64_t A,
                            const double *Xn, int64_t ldx, int64_t Nn, const double *Yn, int64_t ldy, double *E) {
     return predict_common(c, R, Q, K, M, A, A, Xn, ldx, Nn, Yn, ldy, 0, E);
+}
+
+int plsb_sse_prefixes(plsb_ctx_t c, const double *R, const double *Q, int64_t K, int64_t M, int64_t A, const double *Xn,
+                      int64_t ldx, int64_t Nn, const double *Yn, int64_t ldy, double *sse) {
+    return predict_common(c, R, Q, K, M, A, A, Xn, ldx, Nn, Yn, ldy, 0, sse, true);
+}
+
+int plsb_sse(plsb_ctx_t c, const double *R, const double *Q, int64_t K, int64_t M, int64_t comp, const double *Xn,
+             int64_t ldx, int64_t Nn, const double *Yn, int64_t ldy, double *sse) {
+    PLSB_ARG(Nn == 0 || Yn, "Y is null");
+    return predict_common(c, R, Q, K, M, comp, comp, Xn, ldx, Nn, Yn, ldy, 2, sse, true);
+}
+
+int plsb_coefficients(plsb_ctx_t c, const double *R, const double *Q, int64_t K, int64_t M, int64_t comp, double *B) {
+    PLSB_ARG(c && R && Q && B, "null argument");
+    PLSB_ARG(comp >= 0 && K >= 1 && M >= 1, "bad shape");
+    PLSB_CUDA(cudaSetDevice(c->device));
+    Tmp Rd, Qd, Bd;
+    PLSB_TRY(Rd.alloc((size_t)comp * K));
+    PLSB_TRY(Qd.alloc((size_t)comp * M));
+    PLSB_TRY(Bd.alloc((size_t)K * M));
+    PLSB_CUDA(cudaMemcpyAsync(Rd.p, R, (size_t)comp * K * 8, cudaMemcpyHostToDevice, c->stream));
+    PLSB_CUDA(cudaMemcpyAsync(Qd.p, Q, (size_t)comp * M * 8, cudaMemcpyHostToDevice, c->stream));
+    dim3 grid((unsigned)ceil_div(K, 256), (unsigned)M);
+    coefficients_kernel<<<grid, 256, 0, c->stream>>>(Rd.p, Qd.p, (int)K, (int)M, (int)comp, Bd.p);
+    c->launches++;
+    PLSB_CUDA(cudaGetLastError());
+    PLSB_CUDA(cudaMemcpyAsync(B, Bd.p, (size_t)K * M * 8, cudaMemcpyDeviceToHost, c->stream));
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
 }
 
 }  // extern "C"

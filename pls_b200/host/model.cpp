@@ -1,0 +1,285 @@
+// pls_b200/host/model.cpp — PLS::Model on the B200 engine: every method marshals Eigen column-major
+// host buffers into include/plsb.h calls and wraps the real results back into the reference's
+// (complex-typed) return types.  No arithmetic of the fit / predict / CV path happens here.
+//
+// Reference being replaced: src/pls.cpp:323-359 (constructors), 390-437 (plsr), 439-467 (scores,
+// coefficients, fitted_values, residuals, SSE, explained_variance), 469-549 (cv_LOO, cv_NEW_DATA,
+// cv_LSO), 551-580 (print_explained_variance, print_state).
+#include <cassert>
+#include <cmath>
+#include <iomanip>
+#include <thread>
+
+#include <PLS/pls.h>
+
+#include "engine.h"
+
+namespace PLS {
+
+using detail::DeviceMirror;
+using detail::Engine;
+using detail::ok;
+
+namespace {
+// real K x A (column-major) -> the reference's complex matrix type with zero imaginary parts
+Mat2Dc as_complex(const Mat2D &m) { return m.cast<std::complex<float_type>>(); }
+// Eigen::Map-free access: Mat2D is column-major with ld = rows
+inline int64_t ld(const Mat2D &m) { return m.rows() > 0 ? (int64_t)m.rows() : 1; }
+}  // namespace
+
+// ---- constructors (pls.cpp:323-359) ---------------------------------------------------------------
+Model::Model(const size_t &num_predictors, const size_t &num_responses, const METHOD &algorithm,
+             const size_t &max_components)
+    : A(max_components), method(algorithm) {
+    assert(max_components <= num_predictors);
+    P.setZero(num_predictors, A);
+    W.setZero(num_predictors, A);
+    R.setZero(num_predictors, A);
+    Q.setZero(num_responses, A);
+}
+
+Model::Model(const size_t &num_predictors, const size_t &num_responses, const METHOD &algorithm)
+    : Model(num_predictors, num_responses, algorithm, num_predictors) {}
+
+Model::Model(const Mat2D &X, const Mat2D &Y, const METHOD &algorithm, const size_t &max_components)
+    : _X(X), _Y(Y), A(max_components), method(algorithm) {
+    assert(max_components <= static_cast<size_t>(_X.cols()));
+    assert(_X.rows() != 0);
+    assert(_X.rows() == _Y.rows());
+    P.setZero(_X.cols(), A);
+    W.setZero(_X.cols(), A);
+    R.setZero(_X.cols(), A);
+    Q.setZero(_Y.cols(), A);
+    // the device copy of (_X, _Y) made for this fit is kept: cv_LOO / cv_LSO reuse it
+    mirror = std::make_shared<DeviceMirror>();
+    mirror->N = _X.rows(); mirror->K = _X.cols(); mirror->M = _Y.cols();
+    method = algorithm;
+    fit_on(*mirror, _X, _Y, algorithm);
+}
+
+Model::Model(const Mat2D &X, const Mat2D &Y, const METHOD &algorithm) : Model(X, Y, algorithm, X.cols()) {}
+
+// ---- fit (pls.cpp:390-437) ------------------------------------------------------------------------
+void Model::plsr(const Mat2D &X, const Mat2D &Y, const METHOD &algorithm) {
+    if (X.data() == _X.data() && Y.data() == _Y.data() && mirror) {  // refit on the model's own data
+        fit_on(*mirror, X, Y, algorithm);
+        return;
+    }
+    DeviceMirror scratch;  // foreign data: device copy lives for this call only
+    scratch.N = X.rows(); scratch.K = X.cols(); scratch.M = Y.cols();
+    fit_on(scratch, X, Y, algorithm);
+}
+
+void Model::fit_on(DeviceMirror &data, const Mat2D &X, const Mat2D &Y, const METHOD &algorithm) {
+    method = algorithm;
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const int64_t N = X.rows(), K = X.cols(), M = Y.cols();
+    const int meth = algorithm == KERNEL_TYPE2 ? PLSB_KERNEL_TYPE2 : PLSB_KERNEL_TYPE1;
+    const bool wantT = algorithm == KERNEL_TYPE1;
+    Mat2D Wr(K, A), Pr(K, A), Rr(K, A), Qr(M, A), Tr;
+    if (wantT) Tr.resize(N, A);
+    const size_t ndev = e.ndev();
+    if (ndev > 1 && N >= e.shard_min_rows) {
+        // row-sharded fit: every GPU streams its rows, K-length partials are all-reduced
+        e.ensure_comm();
+        data.make_shards(X.data(), ld(X), Y.data(), ld(Y));
+        std::vector<Mat2D> Tpart(ndev);
+        e.parallel([&](size_t i) {
+            const int64_t rows = data.shard_row0[i + 1] - data.shard_row0[i];
+            if (wantT) Tpart[i].resize(rows, A);
+            const bool lead = i == 0;  // the K-sized results are replicated: read them from rank 0 only
+            ok(plsb_fit(data.shard[i], (int64_t)A, meth, lead ? Wr.data() : nullptr, lead ? Pr.data() : nullptr,
+                        lead ? Rr.data() : nullptr, lead ? Qr.data() : nullptr, wantT ? Tpart[i].data() : nullptr),
+               "plsb_fit(sharded)");
+        });
+        if (wantT)
+            for (size_t i = 0; i < ndev; ++i) Tr.middleRows(data.shard_row0[i], Tpart[i].rows()) = Tpart[i];
+        data.drop_shards();
+    } else {
+        plsb_dataset_t ds = data.full_on(0, X.data(), ld(X), Y.data(), ld(Y));
+        ok(plsb_fit(ds, (int64_t)A, meth, Wr.data(), Pr.data(), Rr.data(), Qr.data(), wantT ? Tr.data() : nullptr),
+           "plsb_fit");
+    }
+    W = as_complex(Wr);
+    P = as_complex(Pr);
+    R = as_complex(Rr);
+    Q = as_complex(Qr);
+    if (wantT) T = as_complex(Tr);  // KERNEL_TYPE2 leaves T as it was (pls.cpp:394, 434)
+}
+
+// ---- prediction helpers (pls.cpp:439-467) ---------------------------------------------------------
+const Mat2Dc Model::scores(const Mat2D &X_new, const size_t comp) const {
+    assert(A >= comp);
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const Mat2D Rr = R.real();
+    Mat2D S(X_new.rows(), comp);
+    if (comp > 0)
+        ok(plsb_scores(e.primary(), Rr.data(), Rr.rows(), (int64_t)comp, X_new.data(), ld(X_new), X_new.rows(), S.data()),
+           "plsb_scores");
+    return as_complex(S);
+}
+
+const Mat2Dc Model::loadingsX(const size_t comp) const {
+    assert(A >= comp);
+    return P.leftCols(comp);
+}
+
+const Mat2Dc Model::loadingsY(const size_t comp) const {
+    assert(A >= comp);
+    return Q.leftCols(comp);
+}
+
+const Mat2Dc Model::coefficients(const size_t comp) const {
+    assert(A >= comp);
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const Mat2D Rr = R.real(), Qr = Q.real();
+    Mat2D B(Rr.rows(), Qr.rows());
+    ok(plsb_coefficients(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, B.data()),
+       "plsb_coefficients");
+    return as_complex(B);
+}
+
+const Mat2D Model::fitted_values(const Mat2D &X_new, const size_t comp) const {
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const Mat2D Rr = R.real(), Qr = Q.real();
+    Mat2D F = Mat2D::Zero(X_new.rows(), Qr.rows());
+    if (comp > 0)
+        ok(plsb_fitted(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data(), ld(X_new),
+                       X_new.rows(), nullptr, 1, F.data()),
+           "plsb_fitted");
+    return F;
+}
+
+const Mat2D Model::residuals(const Mat2D &X_new, const Mat2D &Y_new, const size_t comp) const {
+    if (comp == 0) return Y_new;
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const Mat2D Rr = R.real(), Qr = Q.real();
+    Mat2D E(X_new.rows(), Qr.rows());
+    ok(plsb_fitted(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data(), ld(X_new),
+                   X_new.rows(), Y_new.data(), ld(Y_new), E.data()),
+       "plsb_fitted(residuals)");
+    return E;
+}
+
+const Row Model::SSE(const Mat2D &X_new, const Mat2D &Y_new, const size_t comp) const {
+    if (comp == 0) return Y_new.colwise().squaredNorm();
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const Mat2D Rr = R.real(), Qr = Q.real();
+    Row sse(Qr.rows());
+    ok(plsb_sse(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data(), ld(X_new),
+                X_new.rows(), Y_new.data(), ld(Y_new), sse.data()),
+       "plsb_sse");
+    return sse;
+}
+
+const Row Model::explained_variance(const Mat2D &X_new, const Mat2D &Y_new, const size_t comp) const {
+    return (1.0 - (SSE(X_new, Y_new, comp).array() / SST(Y_new).array())).matrix();
+}
+
+// ---- cross-validation (pls.cpp:469-549) -----------------------------------------------------------
+// All folds go to the GPU(s) as one batched job; folds are split across the engine's devices with no
+// communication and every device writes its own rows of the residual block.
+Residual Model::cv_on_device(const std::vector<int64_t> &test_idx, size_t nfolds, size_t test_size,
+                             const char *label) const {
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const int64_t M = _Y.cols(), rows = (int64_t)(nfolds * test_size);
+    const int meth = method == KERNEL_TYPE2 ? PLSB_KERNEL_TYPE2 : PLSB_KERNEL_TYPE1;
+    std::vector<double> E((size_t)(M * (int64_t)A * rows));
+    const size_t ndev = std::min(e.ndev(), std::max<size_t>(nfolds, 1));
+    DeviceMirror &mir = *mirror;
+    if (mir.full.size() < e.ndev()) mir.full.resize(e.ndev(), nullptr);
+    auto work = [&](size_t i) {
+        if (i >= ndev) return;
+        const int64_t f0 = (int64_t)(i * nfolds / ndev), f1 = (int64_t)((i + 1) * nfolds / ndev);
+        plsb_dataset_t ds = mir.full_on(i, _X.data(), ld(_X), _Y.data(), ld(_Y));
+        ok(plsb_cv_folds(ds, (int64_t)A, meth, (int64_t)nfolds, (int64_t)test_size, test_idx.data(), f0, f1 - f0, E.data()),
+           "plsb_cv_folds");
+    };
+    if (ndev == 1) work(0);
+    else e.parallel(work);
+    std::vector<Mat2D> Ev((size_t)M);
+    for (int64_t m = 0; m < M; ++m)
+        Ev[(size_t)m] = Eigen::Map<const Mat2D>(E.data() + (size_t)(m * (int64_t)A * rows), rows, (Eigen::Index)A);
+    return Residual(Ev, label);
+}
+
+Residual Model::cv_LOO() const {
+    const size_t N = _X.rows();
+    std::vector<int64_t> idx(N);
+    std::iota(idx.begin(), idx.end(), int64_t(0));
+    return cv_on_device(idx, N, 1, "LOO");
+}
+
+Residual Model::cv_LSO(const float_type test_fraction, const size_t num_trials, std::mt19937 &rng) const {
+    const size_t N = _X.rows();
+    const size_t test_size = static_cast<size_t>(test_fraction * N + 0.5);
+    const size_t train_size = N - test_size;
+    assert((test_size != 0) and (train_size != 0));
+    // fold lists come from the caller's generator through rand_nchoosek, one persistent permutation
+    // reshuffled per trial (pls.cpp:522-534): the folds and the final state of `rng` match the reference
+    std::vector<Eigen::Index> sample(train_size), complement(test_size), full(N);
+    std::iota(full.begin(), full.end(), 0);
+    std::vector<int64_t> idx(num_trials * test_size);
+    for (size_t rep = 0; rep < num_trials; ++rep) {
+        rand_nchoosek(rng, full, sample, complement);
+        std::copy(complement.begin(), complement.end(), idx.begin() + rep * test_size);
+    }
+    return cv_on_device(idx, num_trials, test_size, "LSO");
+}
+
+Residual Model::cv_NEW_DATA(const Mat2D &X_new, const Mat2D &Y_new) const {
+    assert((X_new.cols() == _X.cols()) and (Y_new.cols() == _Y.cols()));
+    Engine &e = Engine::get();
+    std::lock_guard<std::recursive_mutex> lk(e.mu);
+    const Mat2D Rr = R.real(), Qr = Q.real();
+    const int64_t M = Y_new.cols(), rows = X_new.rows();
+    std::vector<double> E((size_t)(M * (int64_t)A * rows));
+    ok(plsb_predict_residuals(e.primary(), Rr.data(), Qr.data(), Rr.rows(), M, (int64_t)A, X_new.data(), ld(X_new), rows,
+                              Y_new.data(), ld(Y_new), E.data()),
+       "plsb_predict_residuals");
+    std::vector<Mat2D> Ev((size_t)M);
+    for (int64_t m = 0; m < M; ++m)
+        Ev[(size_t)m] = Eigen::Map<const Mat2D>(E.data() + (size_t)(m * (int64_t)A * rows), rows, (Eigen::Index)A);
+    return Residual(Ev, "NEW DATA");
+}
+
+// ---- text output (pls.cpp:551-580): Eigen's operator<< at the stream's precision, like the reference
+void Model::print_explained_variance(const Mat2D &X, const Mat2D &Y, std::ostream &os) const {
+    // one pass over X gives the SSE of every component count (the reference makes 2A passes)
+    Engine &e = Engine::get();
+    Mat2D sse(_Y.cols() ? _Y.cols() : Y.cols(), A);
+    {
+        std::lock_guard<std::recursive_mutex> lk(e.mu);
+        const Mat2D Rr = R.real(), Qr = Q.real();
+        sse.resize(Qr.rows(), A);
+        ok(plsb_sse_prefixes(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)A, X.data(), ld(X), X.rows(),
+                             Y.data(), ld(Y), sse.data()),
+           "plsb_sse_prefixes");
+    }
+    const Row sst = SST(Y);
+    const size_t wd = ceil(std::log10(A));
+    for (size_t ncomp = 1; ncomp <= A; ncomp++) {
+        const Row s = sse.col(ncomp - 1).transpose();
+        const Row ev = (1.0 - (s.array() / sst.array())).matrix();
+        os << std::setw(wd) << ncomp << " components explained variance: " << ev;
+        os << "  - SSE: " << s << std::endl;
+    }
+}
+
+void Model::print_state(std::ostream &os) const {
+    os << "P:" << std::endl << P << std::endl;
+    os << "W:" << std::endl << W << std::endl;
+    os << "R:" << std::endl << R << std::endl;
+    os << "Q:" << std::endl << Q << std::endl;
+    os << "T:" << std::endl << T << std::endl;
+    os << "coefficients:" << std::endl << coefficients() << std::endl;
+}
+
+}  // namespace PLS

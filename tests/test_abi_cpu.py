@@ -54,3 +54,37 @@ def test_lso_folds_match_reference(name, N, trials):
     tr, te = _capi.lso_folds(N, 0.3, trials)          # std::mt19937 default seed, like main.cpp:38
     assert np.array_equal(tr, g["lso_train"].astype(np.int64))
     assert np.array_equal(te, g["lso_test"].astype(np.int64))
+
+
+# ---- the C++ drop-in layer's host-only behaviour (no GPU needed) ------------------------------------
+import subprocess  # noqa: E402
+
+CLI = os.path.join(ROOT, "pls_b200", "PLS")
+needs_cli = pytest.mark.skipif(not os.path.exists(CLI), reason="pls_b200/PLS not built (needs Eigen headers)")
+
+
+@needs_cli
+def test_cli_usage_exits_100():
+    r = subprocess.run([CLI], capture_output=True, text=True)                       # main.cpp:12-16
+    assert r.returncode == 100 and r.stderr.startswith("Usage: ./pls X_data.csv Y_data.csv num_components")
+
+
+@needs_cli
+def test_cli_ragged_csv_exits_1(tmp_path):
+    p = tmp_path / "ragged.csv"
+    p.write_text("1,2,3\n4,5\n")
+    r = subprocess.run([CLI, str(p), str(p), "1"], capture_output=True, text=True)   # pls.cpp:55-58
+    assert r.returncode == 1
+    assert "row 1 has 2 columns, but previous row(s) have 3 columns." in r.stderr
+
+
+@needs_cli
+def test_cli_without_gpu_fails_loudly(tmp_path):
+    """no CPU fallback: without a usable device the fit exits(1) with the engine's error"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    p = tmp_path / "a.csv"
+    p.write_text("1,2\n3,4\n5,7\n")
+    r = subprocess.run([CLI, str(p), str(p), "1"], capture_output=True, text=True)
+    assert r.returncode == 1 and "plsb_ctx_create failed" in r.stderr
