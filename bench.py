@@ -125,7 +125,8 @@ def run_ours(args):
         ctx.comm_init(rank, world, bytes(uid.cpu().numpy().tobytes()))
 
     N, K, M, A = C4["N"], C4["K"], C4["M"], C4["A"]
-    r0, r1 = rank * N // world, (rank + 1) * N // world
+    from pls_b200 import sharding
+    r0, r1 = sharding.row_shard(N, rank, world)
     ds = _capi.Dataset(ctx, synth=(C4["seed"], r0, r1 - r0, K, M, C4["L"]), sharded=world > 1)
 
     def barrier():
