@@ -80,20 +80,34 @@ int launch_rm_to_cm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
 // ------------------------------------------------------------------------------------------------
 // deterministic cross-CTA reduction: out[i] = sum_b part[b*ld + i], b = 0..nb-1 in order
 // ------------------------------------------------------------------------------------------------
+// 32 columns x 8 row groups per CTA: row group y sums partial rows y, y+8, .. with eight independent loads in
+// flight, then the eight group sums are added in group order.  (A one-thread-per-column loop over ~300 rows
+// is a chain of L2 round trips: 54 us between two 2.4 ms passes; this shape takes a few us.)
 __global__ void __launch_bounds__(256) reduce_partials_kernel(const double *__restrict__ part, int64_t ld, int nb,
                                                               int64_t len, double *__restrict__ out) {
-    int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= len) return;
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int b = 0;
-    for (; b + 4 <= nb; b += 4) {
-        s0 += part[(int64_t)b * ld + i];
-        s1 += part[(int64_t)(b + 1) * ld + i];
-        s2 += part[(int64_t)(b + 2) * ld + i];
-        s3 += part[(int64_t)(b + 3) * ld + i];
+    __shared__ double sm[8][33];
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int64_t i = (int64_t)blockIdx.x * 32 + tx;
+    double acc = 0.0;
+    if (i < len) {
+        const double *p = part + i;
+        int b = ty;
+        for (; b + 56 < nb; b += 64) {
+            const double v0 = p[(int64_t)b * ld], v1 = p[(int64_t)(b + 8) * ld], v2 = p[(int64_t)(b + 16) * ld],
+                         v3 = p[(int64_t)(b + 24) * ld], v4 = p[(int64_t)(b + 32) * ld], v5 = p[(int64_t)(b + 40) * ld],
+                         v6 = p[(int64_t)(b + 48) * ld], v7 = p[(int64_t)(b + 56) * ld];
+            acc += ((v0 + v1) + (v2 + v3)) + ((v4 + v5) + (v6 + v7));
+        }
+        for (; b < nb; b += 8) acc += p[(int64_t)b * ld];
     }
-    for (; b < nb; ++b) s0 += part[(int64_t)b * ld + i];
-    out[i] = (s0 + s1) + (s2 + s3);
+    sm[ty][tx] = acc;
+    __syncthreads();
+    if (ty == 0 && i < len) {
+        double t = 0.0;
+#pragma unroll
+        for (int y = 0; y < 8; ++y) t += sm[y][tx];
+        out[i] = t;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -417,8 +431,11 @@ static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, doubl
         kern<<<(unsigned)grid, NT, smem, c->stream>>>(a);
     }
     PLSB_CUDA(cudaGetLastError());
-    reduce_partials_kernel<<<(unsigned)ceil_div(a.ldk + 1, 256), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid,
-                                                                                       a.ldk + 1, out);
+    {
+        ProfScope ps(c, PLSB_PROF_REDUCE);
+        reduce_partials_kernel<<<(unsigned)ceil_div(a.ldk + 1, 32), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid,
+                                                                                          a.ldk + 1, out);
+    }
     PLSB_CUDA(cudaGetLastError());
     c->launches += 2;
     return PLSB_OK;
@@ -487,7 +504,7 @@ static int run_xty(plsb_ctx *c, const plsb_dataset *ds, double *S) {
         }
         PLSB_CUDA(cudaGetLastError());
         const int64_t len = (int64_t)a.mc * a.ldk;
-        reduce_partials_kernel<<<(unsigned)ceil_div(len, 256), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid, len,
+        reduce_partials_kernel<<<(unsigned)ceil_div(len, 32), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid, len,
                                                                                      S + (size_t)m0 * a.ldk);
         PLSB_CUDA(cudaGetLastError());
         c->launches += 2;

@@ -4,7 +4,10 @@
 // pass just finished, then the weight step 403-411 (incl. find_dominant_ev / dominant_eigenvector,
 // 113-141, on the M x M matrix XY'XY) and the r-orthogonalisation 412-416 for the next component.
 // Also here: the KERNEL_TYPE2 product tt = r'XX r, p = XX r (pls.cpp:423-424) as a multi-CTA SYMV.
+#include <cooperative_groups.h>
+
 #include "internal.h"
+#include "step_cluster.cuh"
 #include "step_core.cuh"
 
 namespace plsb {
@@ -22,11 +25,255 @@ __global__ void __launch_bounds__(STEP_NT) step_kernel(const StepArgs s) {
     next_weights<STEP_NT>(s.K, ldk, s.M, an, s.S, s.P, s.R, s.W + (size_t)an * ldk, s.R + (size_t)an * ldk, sh);
 }
 
+// ------------------------------------------------------------------------------------------------
+// The step as a thread-block CLUSTER: 8 CTAs on 8 SMs, each owning a slice of the K axis.
+//
+// The step is a dependency chain between two streaming passes (and the only thing between them that does
+// not shrink when rows are sharded over GPUs), so it is built for latency: one SM reading the ~1 MB of
+// P and R for the orthogonalisation, or shuffling 36 Gram entries across 32 warps, costs tens of us
+// (measured with clock64: Gram 14 us, eigen solver 59 us, orthogonalisation up to 29 us in a 1-CTA kernel).
+// Here every CTA keeps its slice of S in shared memory, dots are reduced warp -> CTA -> cluster through
+// distributed shared memory (each CTA reads the other seven's partials after one cluster barrier, in rank
+// order: deterministic and identical on every CTA), and the tiny eigen problem is solved redundantly by
+// warp 0 of every CTA so no broadcast is needed.
+// ------------------------------------------------------------------------------------------------
+namespace cg = cooperative_groups;
+constexpr int SC_NCTA = 8, SC_NT = 256, SC_NW = SC_NT / 32, SC_KPT = 2;  // K <= 8 * 256 * 2 = 4096
+
+struct StepClLay {
+    int cpc;      // columns per CTA
+    int nvs;      // capacity of one reduction (values)
+    size_t bytes;
+};
+static StepClLay step_cl_layout(int ldk, int M) {
+    StepClLay l;
+    l.cpc = (int)ceil_div(ldk, SC_NCTA);
+    int nv = M * (M + 1) / 2;
+    if (nv < 64) nv = 64;
+    l.nvs = (int)round_up(nv, 32);
+    const int npairs = M * (M + 1) / 2;
+    l.bytes = sizeof(double) * ((size_t)M * l.cpc + (size_t)SC_NW * l.nvs + 3 * (size_t)l.nvs + 3 * (size_t)M * M + M + 8) +
+              (size_t)round_up(2 * npairs, 16);
+    return l;
+}
+
+struct StepClSmem {
+    double *S, *red, *mine, *tot, *G, *B, *C, *q;
+    unsigned char *pu, *pv;
+    int nvs, phase;
+};
+
+// CTA-level then cluster-level sum of nv per-thread values; the totals land in sm.tot on every CTA
+template <typename F>
+__device__ __forceinline__ void cl_reduce(cg::cluster_group &cluster, StepClSmem &sm, int nv, F val) {
+    const int tid = threadIdx.x, warp = tid >> 5;
+    warp_reduce_many(nv, val, sm.red + (size_t)warp * sm.nvs);
+    __syncthreads();
+    double *mine = sm.mine + (size_t)(sm.phase & 1) * sm.nvs;
+    for (int v = tid; v < nv; v += SC_NT) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < SC_NW; ++w) t += sm.red[(size_t)w * sm.nvs + v];
+        mine[v] = t;
+    }
+    cluster.sync();
+    for (int v = tid; v < nv; v += SC_NT) {
+        double t = 0.0;
+#pragma unroll
+        for (int c = 0; c < SC_NCTA; ++c) t += cluster.map_shared_rank(mine, c)[v];
+        sm.tot[v] = t;
+    }
+    __syncthreads();
+    sm.phase++;
+}
+
+__global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s, const int cpc, const int nvs) {
+    extern __shared__ __align__(16) double sc_smem[];
+    cg::cluster_group cluster = cg::this_cluster();
+    const int K = s.K, ldk = s.ldk, M = s.M;
+    const int npairs = M * (M + 1) / 2;
+    StepClSmem sm;
+    sm.S = sc_smem;                              // M x cpc slice of S
+    sm.red = sm.S + (size_t)M * cpc;             // [warps][nvs]
+    sm.mine = sm.red + (size_t)SC_NW * nvs;      // [2][nvs] this CTA's partials (double buffered, read remotely)
+    sm.tot = sm.mine + 2 * (size_t)nvs;          // [nvs] cluster totals
+    sm.G = sm.tot + nvs; sm.B = sm.G + M * M; sm.C = sm.B + M * M; sm.q = sm.C + M * M;
+    sm.pu = reinterpret_cast<unsigned char *>(sm.q + M + 8); sm.pv = sm.pu + npairs;
+    sm.nvs = nvs; sm.phase = 0;
+    const int tid = threadIdx.x, warp = tid >> 5;
+    const int rank = (int)cluster.block_rank();
+    const int c0 = rank * cpc;                   // first column of this CTA
+    int kl[SC_KPT], kg[SC_KPT];
+    bool live[SC_KPT], wr[SC_KPT];               // live: a real column; wr: real or padding (gets zero)
+#pragma unroll
+    for (int j = 0; j < SC_KPT; ++j) {
+        kl[j] = tid + SC_NT * j;
+        kg[j] = c0 + kl[j];
+        live[j] = kl[j] < cpc && kg[j] < K;
+        wr[j] = kl[j] < cpc && kg[j] < ldk;
+    }
+    for (int d = tid; d < npairs; d += SC_NT) {  // (u, v) of Gram entry d, u <= v
+        int u = 0, rem = d;
+        while (rem >= M - u) { rem -= M - u; ++u; }
+        sm.pu[d] = (unsigned char)u;
+        sm.pv[d] = (unsigned char)(u + rem);
+    }
+#pragma unroll
+    for (int j = 0; j < SC_KPT; ++j)
+        if (wr[j])
+            for (int m = 0; m < M; ++m) sm.S[(size_t)m * cpc + kl[j]] = s.S[(size_t)m * ldk + kg[j]];
+    __syncthreads();  // pair table visible (each thread touches only its own columns of sm.S)
+    const int an = s.a + 1;
+    double x[SC_KPT];  // r_a, later w
+    if (s.a >= 0) {
+        const double tt = s.g[ldk];
+        double p[SC_KPT];
+        double *Pa = s.P + (size_t)s.a * ldk;
+        const double *Ra = s.R + (size_t)s.a * ldk;
+#pragma unroll
+        for (int j = 0; j < SC_KPT; ++j) {
+            p[j] = live[j] ? s.g[kg[j]] / tt : 0.0;
+            x[j] = live[j] ? Ra[kg[j]] : 0.0;
+            if (wr[j]) Pa[kg[j]] = p[j];
+        }
+        // q = S'r / tt   (pls.cpp:428) with S as it was before this component's deflation
+        cl_reduce(cluster, sm, M, [&](int m) {
+            double acc = 0.0;
+#pragma unroll
+            for (int j = 0; j < SC_KPT; ++j) if (live[j]) acc = fma(sm.S[(size_t)m * cpc + kl[j]], x[j], acc);
+            return acc;
+        });
+        if (rank == 0 && tid < M) s.Q[(size_t)s.a * M + tid] = sm.tot[tid] / tt;
+        // S -= tt p q'   (pls.cpp:429)
+        for (int m = 0; m < M; ++m) {
+            const double qm = sm.tot[m] / tt;
+#pragma unroll
+            for (int j = 0; j < SC_KPT; ++j)
+                if (live[j]) sm.S[(size_t)m * cpc + kl[j]] -= (tt * p[j]) * qm;
+        }
+    }
+    if (an >= s.A) {
+        cluster.sync();  // nobody may leave while a neighbour can still read its shared memory
+        return;
+    }
+    // the deflated slice goes back to global memory for the next step; nothing below waits on it
+#pragma unroll
+    for (int j = 0; j < SC_KPT; ++j)
+        if (wr[j] && s.a >= 0)
+            for (int m = 0; m < M; ++m) s.S[(size_t)m * ldk + kg[j]] = sm.S[(size_t)m * cpc + kl[j]];
+    // ---- weight vector of component an (pls.cpp:403-411) ----
+    if (M == 1) {
+#pragma unroll
+        for (int j = 0; j < SC_KPT; ++j) x[j] = live[j] ? sm.S[kl[j]] : 0.0;
+    } else {
+        cl_reduce(cluster, sm, npairs, [&](int d) {
+            const double *su = sm.S + (size_t)sm.pu[d] * cpc, *sv = sm.S + (size_t)sm.pv[d] * cpc;
+            double acc = 0.0;
+#pragma unroll
+            for (int j = 0; j < SC_KPT; ++j) if (live[j]) acc = fma(su[kl[j]], sv[kl[j]], acc);
+            return acc;
+        });
+        if (warp == 0) {
+            for (int d = tid; d < npairs; d += 32) {
+                sm.G[sm.pu[d] * M + sm.pv[d]] = sm.tot[d];
+                sm.G[sm.pv[d] * M + sm.pu[d]] = sm.tot[d];
+            }
+            __syncwarp();
+            dominant_eigvec_warp(sm.G, sm.B, sm.C, M, sm.q);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < SC_KPT; ++j) {
+            double acc = 0.0;
+            if (live[j])
+                for (int m = 0; m < M; ++m) acc = fma(sm.S[(size_t)m * cpc + kl[j]], sm.q[m], acc);
+            x[j] = acc;
+        }
+    }
+    cl_reduce(cluster, sm, 1, [&](int) {
+        double acc = 0.0;
+#pragma unroll
+        for (int j = 0; j < SC_KPT; ++j) acc = fma(x[j], x[j], acc);
+        return acc;
+    });
+    {   // w /= sqrt(w'w)   (pls.cpp:411)
+        const double nrm = sqrt(sm.tot[0]);
+        double *Wn = s.W + (size_t)an * ldk;
+#pragma unroll
+        for (int j = 0; j < SC_KPT; ++j) {
+            x[j] = live[j] ? x[j] / nrm : 0.0;
+            if (wr[j]) Wn[kg[j]] = x[j];
+        }
+    }
+    // ---- r = w - sum_j (p_j'w) r_j   (pls.cpp:412-416), subtraction order j = 0..an-1 ----
+    double r[SC_KPT];
+#pragma unroll
+    for (int j = 0; j < SC_KPT; ++j) r[j] = x[j];
+    for (int j0 = 0; j0 < an; j0 += nvs) {
+        const int nj = an - j0 < nvs ? an - j0 : nvs;
+        cl_reduce(cluster, sm, nj, [&](int jj) {
+            const double *Pj = s.P + (size_t)(j0 + jj) * ldk;
+            double acc = 0.0;
+#pragma unroll
+            for (int j = 0; j < SC_KPT; ++j) if (live[j]) acc = fma(Pj[kg[j]], x[j], acc);
+            return acc;
+        });
+        int jj = 0;
+        for (; jj + 4 <= nj; jj += 4) {  // four independent loads in flight per column
+            const double *Rj = s.R + (size_t)(j0 + jj) * ldk;
+#pragma unroll
+            for (int j = 0; j < SC_KPT; ++j)
+                if (live[j]) {
+                    const double r0 = Rj[kg[j]], r1 = Rj[kg[j] + ldk], r2 = Rj[kg[j] + 2 * (size_t)ldk], r3 = Rj[kg[j] + 3 * (size_t)ldk];
+                    r[j] -= sm.tot[jj] * r0;
+                    r[j] -= sm.tot[jj + 1] * r1;
+                    r[j] -= sm.tot[jj + 2] * r2;
+                    r[j] -= sm.tot[jj + 3] * r3;
+                }
+        }
+        for (; jj < nj; ++jj) {
+            const double *Rj = s.R + (size_t)(j0 + jj) * ldk;
+#pragma unroll
+            for (int j = 0; j < SC_KPT; ++j) if (live[j]) r[j] -= sm.tot[jj] * Rj[kg[j]];
+        }
+    }
+    double *Rn = s.R + (size_t)an * ldk;
+#pragma unroll
+    for (int j = 0; j < SC_KPT; ++j) if (wr[j]) Rn[kg[j]] = r[j];
+    cluster.sync();
+}
+
+static int launch_step_cluster(plsb_ctx *c, const StepArgs &s) {
+    const StepClLay lay = step_cl_layout(s.ldk, s.M);
+    PLSB_CUDA(cudaFuncSetAttribute(step_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lay.bytes));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(SC_NCTA);
+    cfg.blockDim = dim3(SC_NT);
+    cfg.dynamicSmemBytes = lay.bytes;
+    cfg.stream = c->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = SC_NCTA;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    {
+        ProfScope ps(c, PLSB_PROF_STEP);
+        PLSB_CUDA(cudaLaunchKernelEx(&cfg, step_cluster_kernel, s, lay.cpc, lay.nvs));
+    }
+    c->launches++;
+    return PLSB_OK;
+}
+
 int launch_step(plsb_ctx *c, const StepArgs &s) {
     if (s.M > PLSB_MAX_M) {
         set_error("M=%d responses exceed the in-kernel eigen solver limit (%d)", s.M, PLSB_MAX_M);
         return PLSB_ERR_UNSUPPORTED;
     }
+    const bool force_v1 = getenv("PLSB_STEP_V1") != nullptr;  // A/B switch for tools/devbench.py
+    if (!force_v1 && s.ldk <= SC_NCTA * SC_NT * SC_KPT && step_cl_layout(s.ldk, s.M).bytes <= c->smem_optin)
+        return launch_step_cluster(c, s);
     {
         ProfScope ps(c, PLSB_PROF_STEP);
         step_kernel<<<1, STEP_NT, 0, c->stream>>>(s);

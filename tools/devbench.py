@@ -16,11 +16,9 @@ t0 = time.time()
 ds = _capi.Dataset(ctx, synth=(20260004, 0, N, K, M, 16))
 print(f"synth {N}x{K} in {time.time()-t0:.2f}s", flush=True)
 ctx.profile(True)
-variants = [dict(), dict(PLSB_PASS_RB="4"), dict(PLSB_PASS_STAGES="3"), dict(PLSB_PASS_STAGES="2"),
-            dict(PLSB_PASS_CTAS_PER_SM="1", PLSB_PASS_STAGES="6"), dict(PLSB_PASS_RB="4", PLSB_PASS_CTAS_PER_SM="1", PLSB_PASS_STAGES="3"),
-            dict(PLSB_PASS_CTAS_PER_SM="3", PLSB_PASS_STAGES="2")]
+variants = [dict(), dict(PLSB_STEP_V1="1"), dict(PLSB_PASS_RB="4"), dict(PLSB_PASS_STAGES="3")]
 for v in variants:
-    for k in ("PLSB_PASS_RB", "PLSB_PASS_STAGES", "PLSB_PASS_CTAS_PER_SM"):
+    for k in ("PLSB_PASS_RB", "PLSB_PASS_STAGES", "PLSB_PASS_CTAS_PER_SM", "PLSB_STEP_V1"):
         os.environ.pop(k, None)
     os.environ.update(v)
     ds.fit_nocopy(A, 0)          # warm
@@ -32,11 +30,11 @@ for v in variants:
     ctx.sync()
     wall = (time.time() - t0) / reps
     pf, npf = ctx.profile_get("pass_fused"); px, npx = ctx.profile_get("pass_xty")
-    stp, nst = ctx.profile_get("step"); tot, nt = ctx.profile_get("fit_total")
+    stp, nst = ctx.profile_get("step"); tot, nt = ctx.profile_get("fit_total"); rd, nrd = ctx.profile_get("reduce")
     gb = N * K * 8 / 1e9
     print(f"{v}: fit {wall*1e3:.1f} ms wall, device {tot/max(nt,1):.1f} ms | fused pass {pf/max(npf,1):.3f} ms = "
           f"{gb/(pf/max(npf,1)/1e3):.0f} GB/s | xty {px/max(npx,1):.3f} ms = {gb/(px/max(npx,1)/1e3):.0f} GB/s | "
-          f"step {stp/max(nst,1)*1e3:.1f} us", flush=True)
+          f"step {stp/max(nst,1)*1e3:.1f} us | reduce {rd/max(nrd,1)*1e3:.1f} us", flush=True)
 if "--type2" in sys.argv:
     ctx.profile_reset()
     ds.fit_nocopy(A, 1)
