@@ -74,6 +74,7 @@ struct StepArgs {
     const double *g;   // ldk + 1: X'(X r_a) and tt
     double *W, *P, *R; // A x ldk each (column a at [a*ldk])
     double *Q;         // A x M
+    long long *trace;  // dev tool (PLSB_STEP_TRACE): globaltimer ns at phase boundaries, or null
 };
 int launch_step(plsb_ctx *c, const StepArgs &s);
 

@@ -52,41 +52,73 @@ static StepClLay step_cl_layout(int ldk, int M) {
     if (nv < 64) nv = 64;
     l.nvs = (int)round_up(nv, 32);
     const int npairs = M * (M + 1) / 2;
-    l.bytes = sizeof(double) * ((size_t)M * l.cpc + (size_t)SC_NW * l.nvs + 3 * (size_t)l.nvs + 3 * (size_t)M * M + M + 8) +
+    l.bytes = sizeof(double) * ((size_t)M * l.cpc + (size_t)SC_NW * l.nvs + (2 * SC_NCTA + 1) * (size_t)l.nvs + (size_t)M * M + 2048 + M + 8) +
               (size_t)round_up(2 * npairs, 16);
     return l;
 }
 
 struct StepClSmem {
-    double *S, *red, *mine, *tot, *G, *B, *C, *q;
+    double *S, *red, *gather, *tot, *G, *B, *C, *q;
+    uint64_t *bar;          // two mbarriers (one per exchange parity)
     unsigned char *pu, *pv;
-    int nvs, phase;
+    int nvs, phase, rank;
 };
 
-// CTA-level then cluster-level sum of nv per-thread values; the totals land in sm.tot on every CTA
+__device__ __forceinline__ uint32_t cluster_map(const void *smem_ptr, int cta_rank) {
+    uint32_t out;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(out) : "r"(smem_u32(smem_ptr)), "r"(cta_rank));
+    return out;
+}
+// asynchronous 8-byte store into another CTA's shared memory; the destination CTA's mbarrier counts the bytes
+__device__ __forceinline__ void st_async_f64(uint32_t remote_addr, double v, uint32_t remote_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(remote_addr),
+                 "l"(__double_as_longlong(v)), "r"(remote_bar)
+                 : "memory");
+}
+__device__ __forceinline__ void cluster_barrier() {
+    asm volatile("barrier.cluster.arrive.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
+}
+
+// CTA-level then cluster-level sum of nv per-thread values; the totals land in sm.tot on every CTA.
+// Exchange: every CTA pushes its nv partial sums into a slot of every CTA's `gather` array with st.async; the
+// bytes are counted by the destination's mbarrier, so one wait replaces a cluster-wide barrier (whose release
+// fence, MEMBAR.ALL.GPU in SASS, would also wait for this kernel's outstanding global stores each time).
+// Slots and barriers alternate with the exchange parity: traffic of exchange n+2 can only start after every
+// CTA has finished reading exchange n (it has sent n+1 since), so two sets suffice.  Sums run in rank order.
 template <typename F>
-__device__ __forceinline__ void cl_reduce(cg::cluster_group &cluster, StepClSmem &sm, int nv, F val) {
+__device__ __forceinline__ void cl_reduce(StepClSmem &sm, int nv, F val) {
     const int tid = threadIdx.x, warp = tid >> 5;
+    const int par = sm.phase & 1;
+    uint64_t *bar = sm.bar + par;
+    double *gather = sm.gather + (size_t)par * SC_NCTA * sm.nvs;
+    if (tid == 0) mbar_arrive_expect_tx(bar, (uint32_t)(nv * sizeof(double) * SC_NCTA));
     warp_reduce_many(nv, val, sm.red + (size_t)warp * sm.nvs);
     __syncthreads();
-    double *mine = sm.mine + (size_t)(sm.phase & 1) * sm.nvs;
     for (int v = tid; v < nv; v += SC_NT) {
         double t = 0.0;
 #pragma unroll
         for (int w = 0; w < SC_NW; ++w) t += sm.red[(size_t)w * sm.nvs + v];
-        mine[v] = t;
+        double *slot = gather + (size_t)sm.rank * sm.nvs + v;
+#pragma unroll
+        for (int c = 0; c < SC_NCTA; ++c) st_async_f64(cluster_map(slot, c), t, cluster_map(bar, c));
     }
-    cluster.sync();
+    mbar_wait(bar, (uint32_t)((sm.phase >> 1) & 1));
     for (int v = tid; v < nv; v += SC_NT) {
         double t = 0.0;
 #pragma unroll
-        for (int c = 0; c < SC_NCTA; ++c) t += cluster.map_shared_rank(mine, c)[v];
+        for (int c = 0; c < SC_NCTA; ++c) t += gather[(size_t)c * sm.nvs + v];
         sm.tot[v] = t;
     }
     __syncthreads();
     sm.phase++;
 }
 
+__device__ __forceinline__ long long sc_now() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define SC_TRACE(i) do { if (s.trace && threadIdx.x == 0 && blockIdx.x == 0) s.trace[i] = sc_now(); } while (0)
 __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s, const int cpc, const int nvs) {
     extern __shared__ __align__(16) double sc_smem[];
     cg::cluster_group cluster = cg::this_cluster();
@@ -95,23 +127,36 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
     StepClSmem sm;
     sm.S = sc_smem;                              // M x cpc slice of S
     sm.red = sm.S + (size_t)M * cpc;             // [warps][nvs]
-    sm.mine = sm.red + (size_t)SC_NW * nvs;      // [2][nvs] this CTA's partials (double buffered, read remotely)
-    sm.tot = sm.mine + 2 * (size_t)nvs;          // [nvs] cluster totals
-    sm.G = sm.tot + nvs; sm.B = sm.G + M * M; sm.C = sm.B + M * M; sm.q = sm.C + M * M;
+    sm.gather = sm.red + (size_t)SC_NW * nvs;    // [2][ctas][nvs] partial sums pushed here by every CTA
+    sm.tot = sm.gather + 2 * (size_t)SC_NCTA * nvs;  // [nvs] cluster totals
+    sm.G = sm.tot + nvs; sm.B = sm.G + M * M; sm.C = sm.B + 1024; sm.q = sm.C + 1024;  // B, C: up to 32 x 32 padded
+    sm.bar = reinterpret_cast<uint64_t *>(sm.q + M);  // 2 of the 8 spare doubles
     sm.pu = reinterpret_cast<unsigned char *>(sm.q + M + 8); sm.pv = sm.pu + npairs;
     sm.nvs = nvs; sm.phase = 0;
     const int tid = threadIdx.x, warp = tid >> 5;
     const int rank = (int)cluster.block_rank();
+    sm.rank = rank;
+    if (tid == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        mbar_fence_init();
+    }
     const int c0 = rank * cpc;                   // first column of this CTA
     int kl[SC_KPT], kg[SC_KPT];
+    int klc[SC_KPT], kgc[SC_KPT];                // the same, clamped to a valid column when the slot is dead
     bool live[SC_KPT], wr[SC_KPT];               // live: a real column; wr: real or padding (gets zero)
+    double lv[SC_KPT];                           // 1.0 / 0.0 mask of live
 #pragma unroll
     for (int j = 0; j < SC_KPT; ++j) {
         kl[j] = tid + SC_NT * j;
         kg[j] = c0 + kl[j];
         live[j] = kl[j] < cpc && kg[j] < K;
         wr[j] = kl[j] < cpc && kg[j] < ldk;
+        klc[j] = live[j] ? kl[j] : 0;
+        kgc[j] = live[j] ? kg[j] : 0;
+        lv[j] = live[j] ? 1.0 : 0.0;
     }
+    SC_TRACE(0);
     for (int d = tid; d < npairs; d += SC_NT) {  // (u, v) of Gram entry d, u <= v
         int u = 0, rem = d;
         while (rem >= M - u) { rem -= M - u; ++u; }
@@ -123,6 +168,8 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
         if (wr[j])
             for (int m = 0; m < M; ++m) sm.S[(size_t)m * cpc + kl[j]] = s.S[(size_t)m * ldk + kg[j]];
     __syncthreads();  // pair table visible (each thread touches only its own columns of sm.S)
+    cluster_barrier();  // every CTA's mbarriers are initialised before any remote traffic can reach them
+    SC_TRACE(1);
     const int an = s.a + 1;
     double x[SC_KPT];  // r_a, later w
     if (s.a >= 0) {
@@ -137,12 +184,13 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
             if (wr[j]) Pa[kg[j]] = p[j];
         }
         // q = S'r / tt   (pls.cpp:428) with S as it was before this component's deflation
-        cl_reduce(cluster, sm, M, [&](int m) {
+        cl_reduce(sm, M, [&](int m) {
             double acc = 0.0;
 #pragma unroll
-            for (int j = 0; j < SC_KPT; ++j) if (live[j]) acc = fma(sm.S[(size_t)m * cpc + kl[j]], x[j], acc);
+            for (int j = 0; j < SC_KPT; ++j) acc = fma(sm.S[(size_t)m * cpc + klc[j]], x[j], acc);  // x is 0 on dead slots
             return acc;
         });
+        SC_TRACE(2);
         if (rank == 0 && tid < M) s.Q[(size_t)s.a * M + tid] = sm.tot[tid] / tt;
         // S -= tt p q'   (pls.cpp:429)
         for (int m = 0; m < M; ++m) {
@@ -152,10 +200,10 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
                 if (live[j]) sm.S[(size_t)m * cpc + kl[j]] -= (tt * p[j]) * qm;
         }
     }
-    if (an >= s.A) {
-        cluster.sync();  // nobody may leave while a neighbour can still read its shared memory
-        return;
-    }
+    // (a CTA may exit as soon as it is done: it has waited for all traffic addressed to it, and nobody reads
+    //  its shared memory — data is pushed, never pulled)
+    if (an >= s.A) return;
+    SC_TRACE(3);
     // the deflated slice goes back to global memory for the next step; nothing below waits on it
 #pragma unroll
     for (int j = 0; j < SC_KPT; ++j)
@@ -166,22 +214,24 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
 #pragma unroll
         for (int j = 0; j < SC_KPT; ++j) x[j] = live[j] ? sm.S[kl[j]] : 0.0;
     } else {
-        cl_reduce(cluster, sm, npairs, [&](int d) {
+        cl_reduce(sm, npairs, [&](int d) {
             const double *su = sm.S + (size_t)sm.pu[d] * cpc, *sv = sm.S + (size_t)sm.pv[d] * cpc;
             double acc = 0.0;
 #pragma unroll
-            for (int j = 0; j < SC_KPT; ++j) if (live[j]) acc = fma(su[kl[j]], sv[kl[j]], acc);
+            for (int j = 0; j < SC_KPT; ++j) acc = fma(su[klc[j]] * lv[j], sv[klc[j]], acc);
             return acc;
         });
+        SC_TRACE(4);
         if (warp == 0) {
             for (int d = tid; d < npairs; d += 32) {
                 sm.G[sm.pu[d] * M + sm.pv[d]] = sm.tot[d];
                 sm.G[sm.pv[d] * M + sm.pu[d]] = sm.tot[d];
             }
             __syncwarp();
-            dominant_eigvec_warp(sm.G, sm.B, sm.C, M, sm.q);
+            dominant_eigvec_warp(sm.G, sm.B, sm.C, M, sm.q, (s.trace && blockIdx.x == 0) ? s.trace + 10 : nullptr);
         }
         __syncthreads();
+        SC_TRACE(5);
 #pragma unroll
         for (int j = 0; j < SC_KPT; ++j) {
             double acc = 0.0;
@@ -190,12 +240,13 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
             x[j] = acc;
         }
     }
-    cl_reduce(cluster, sm, 1, [&](int) {
+    cl_reduce(sm, 1, [&](int) {
         double acc = 0.0;
 #pragma unroll
         for (int j = 0; j < SC_KPT; ++j) acc = fma(x[j], x[j], acc);
         return acc;
     });
+    SC_TRACE(6);
     {   // w /= sqrt(w'w)   (pls.cpp:411)
         const double nrm = sqrt(sm.tot[0]);
         double *Wn = s.W + (size_t)an * ldk;
@@ -211,36 +262,38 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
     for (int j = 0; j < SC_KPT; ++j) r[j] = x[j];
     for (int j0 = 0; j0 < an; j0 += nvs) {
         const int nj = an - j0 < nvs ? an - j0 : nvs;
-        cl_reduce(cluster, sm, nj, [&](int jj) {
+        cl_reduce(sm, nj, [&](int jj) {
             const double *Pj = s.P + (size_t)(j0 + jj) * ldk;
             double acc = 0.0;
 #pragma unroll
-            for (int j = 0; j < SC_KPT; ++j) if (live[j]) acc = fma(Pj[kg[j]], x[j], acc);
+            for (int j = 0; j < SC_KPT; ++j) acc = fma(Pj[kgc[j]], x[j], acc);  // x is 0 on dead slots
             return acc;
         });
+        SC_TRACE(7);
         int jj = 0;
-        for (; jj + 4 <= nj; jj += 4) {  // four independent loads in flight per column
+        for (; jj + 8 <= nj; jj += 8) {  // eight independent loads in flight per column
             const double *Rj = s.R + (size_t)(j0 + jj) * ldk;
 #pragma unroll
-            for (int j = 0; j < SC_KPT; ++j)
-                if (live[j]) {
-                    const double r0 = Rj[kg[j]], r1 = Rj[kg[j] + ldk], r2 = Rj[kg[j] + 2 * (size_t)ldk], r3 = Rj[kg[j] + 3 * (size_t)ldk];
-                    r[j] -= sm.tot[jj] * r0;
-                    r[j] -= sm.tot[jj + 1] * r1;
-                    r[j] -= sm.tot[jj + 2] * r2;
-                    r[j] -= sm.tot[jj + 3] * r3;
-                }
+            for (int j = 0; j < SC_KPT; ++j) {
+                double rv[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) rv[u] = Rj[kgc[j] + (size_t)u * ldk];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) r[j] -= sm.tot[jj + u] * rv[u];
+            }
         }
         for (; jj < nj; ++jj) {
             const double *Rj = s.R + (size_t)(j0 + jj) * ldk;
 #pragma unroll
-            for (int j = 0; j < SC_KPT; ++j) if (live[j]) r[j] -= sm.tot[jj] * Rj[kg[j]];
+            for (int j = 0; j < SC_KPT; ++j) r[j] -= sm.tot[jj] * Rj[kgc[j]];
         }
     }
+#pragma unroll
+    for (int j = 0; j < SC_KPT; ++j) r[j] *= lv[j];
     double *Rn = s.R + (size_t)an * ldk;
 #pragma unroll
     for (int j = 0; j < SC_KPT; ++j) if (wr[j]) Rn[kg[j]] = r[j];
-    cluster.sync();
+    SC_TRACE(9);
 }
 
 static int launch_step_cluster(plsb_ctx *c, const StepArgs &s) {
@@ -258,6 +311,23 @@ static int launch_step_cluster(plsb_ctx *c, const StepArgs &s) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    if (getenv("PLSB_STEP_TRACE")) {  // dev tool (tools/steptrace.py): phase timestamps of this launch on stderr
+        static long long *tr = nullptr;
+        if (!tr) PLSB_CUDA(cudaMalloc(&tr, 16 * sizeof(long long)));
+        PLSB_CUDA(cudaMemsetAsync(tr, 0, 16 * sizeof(long long), c->stream));
+        StepArgs st = s;
+        st.trace = tr;
+        PLSB_CUDA(cudaLaunchKernelEx(&cfg, step_cluster_kernel, st, lay.cpc, lay.nvs));
+        long long h[16];
+        PLSB_CUDA(cudaMemcpyAsync(h, tr, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+        PLSB_CUDA(cudaStreamSynchronize(c->stream));
+        fprintf(stderr, "step a=%d ns:", s.a);
+        for (int i = 1; i < 10; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[0] : -1);
+        fprintf(stderr, " | squarings %lld", h[10]);
+        fprintf(stderr, "\n");
+        c->launches++;
+        return PLSB_OK;
+    }
     {
         ProfScope ps(c, PLSB_PROF_STEP);
         PLSB_CUDA(cudaLaunchKernelEx(&cfg, step_cluster_kernel, s, lay.cpc, lay.nvs));
