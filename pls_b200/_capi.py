@@ -18,7 +18,7 @@ i64 = C.c_int64
 
 # symbols include/plsb.h declares (tests check that the library exports every one)
 SYMBOLS = [
-    "plsb_last_error", "plsb_version", "plsb_device_count", "plsb_ctx_create", "plsb_ctx_destroy", "plsb_ctx_sync",
+    "plsb_last_error", "plsb_version", "plsb_device_count", "plsb_ctx_create", "plsb_ctx_destroy", "plsb_ctx_sync", "plsb_ctx_trim",
     "plsb_comm_unique_id", "plsb_comm_init", "plsb_comm_allreduce_test",
     "plsb_dataset_create", "plsb_dataset_create_device", "plsb_dataset_create_synth", "plsb_dataset_destroy",
     "plsb_dataset_shape", "plsb_dataset_download", "plsb_dataset_set_sharded",
@@ -88,6 +88,9 @@ class Context:
 
     def sync(self):
         check(lib().plsb_ctx_sync(self.h))
+
+    def trim(self):
+        check(lib().plsb_ctx_trim(self.h))
 
     # -- communicator (row-sharded fits) -------------------------------------------------------
     @staticmethod

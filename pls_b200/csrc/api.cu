@@ -60,16 +60,35 @@ int cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
     return PLSB_ERR_CUDA;
 }
 
+int dev_alloc(plsb_ctx *c, void **p, size_t bytes) {
+    PLSB_CUDA(cudaMallocAsync(p, bytes ? bytes : 8, c->stream));
+    return PLSB_OK;
+}
+void dev_free(plsb_ctx *c, void *p) {
+    if (p) cudaFreeAsync(p, c->stream);
+}
+int dev_mem_available(plsb_ctx *c, size_t *bytes) {
+    size_t free_b = 0, total_b = 0;
+    PLSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    cudaMemPool_t pool;
+    uint64_t reserved = 0, used = 0;
+    if (cudaDeviceGetDefaultMemPool(&pool, c->device) == cudaSuccess &&
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved) == cudaSuccess &&
+        cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used) == cudaSuccess && reserved > used)
+        free_b += (size_t)(reserved - used);
+    *bytes = free_b;
+    return PLSB_OK;
+}
+
 int ensure_part(plsb_ctx *c, size_t bytes) {
     if (bytes <= c->part_bytes) return PLSB_OK;
     if (c->part) {
-        PLSB_CUDA(cudaStreamSynchronize(c->stream));
-        PLSB_CUDA(cudaFree(c->part));
+        dev_free(c, c->part);  // stream-ordered: kernels already queued on the stream keep their scratch
         c->part = nullptr;
         c->part_bytes = 0;
     }
     bytes = (size_t)round_up((int64_t)bytes, 1 << 20);
-    PLSB_CUDA(cudaMalloc(&c->part, bytes));
+    PLSB_TRY(dev_alloc(c, (void **)&c->part, bytes));
     c->part_bytes = bytes;
     return PLSB_OK;
 }
@@ -139,6 +158,12 @@ int plsb_ctx_create(int device, plsb_ctx_t *out) {
     c->smem_optin = prop.sharedMemPerBlockOptin;
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete c; return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__); }
+    {   // keep freed blocks in the pool (see dev_alloc)
+        cudaMemPool_t pool;
+        uint64_t keep = UINT64_MAX;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess)
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     *out = c;
     return PLSB_OK;
 }
@@ -150,9 +175,20 @@ int plsb_ctx_destroy(plsb_ctx_t c) {
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto e : c->pool) cudaEventDestroy(e);
-    if (c->part) cudaFree(c->part);
+    if (c->part) cudaFreeAsync(c->part, c->stream);
+    cudaStreamSynchronize(c->stream);
     cudaStreamDestroy(c->stream);
     delete c;
+    return PLSB_OK;
+}
+
+int plsb_ctx_trim(plsb_ctx_t c) {
+    PLSB_ARG(c, "ctx is null");
+    PLSB_CUDA(cudaSetDevice(c->device));
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    cudaMemPool_t pool;
+    PLSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, c->device));
+    PLSB_CUDA(cudaMemPoolTrimTo(pool, 0));
     return PLSB_OK;
 }
 
@@ -228,7 +264,7 @@ extern "C" int plsb_comm_allreduce_test(plsb_ctx_t c, double *host_buf, int64_t 
     PLSB_ARG(c && host_buf && n > 0, "bad argument");
     PLSB_CUDA(cudaSetDevice(c->device));
     double *d = nullptr;
-    PLSB_CUDA(cudaMalloc(&d, sizeof(double) * n));
+    PLSB_TRY(plsb::dev_alloc(c, (void **)&d, sizeof(double) * n));
     PLSB_CUDA(cudaMemcpyAsync(d, host_buf, sizeof(double) * n, cudaMemcpyHostToDevice, c->stream));
     int rc = plsb::allreduce_sum(c, d, (size_t)n);
     if (rc == PLSB_OK) {
@@ -236,6 +272,6 @@ extern "C" int plsb_comm_allreduce_test(plsb_ctx_t c, double *host_buf, int64_t 
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if (e != cudaSuccess) rc = cuda_fail(e, "allreduce_test copy", __FILE__, __LINE__);
     }
-    cudaFree(d);
+    plsb::dev_free(c, d);
     return rc;
 }

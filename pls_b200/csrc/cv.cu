@@ -91,9 +91,11 @@ __global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
 }
 
 struct CvBuf {
+    plsb_ctx *c;
     void *p = nullptr;
-    ~CvBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { PLSB_CUDA(cudaMalloc(&p, bytes ? bytes : 8)); return PLSB_OK; }
+    explicit CvBuf(plsb_ctx *ctx) : c(ctx) {}
+    ~CvBuf() { dev_free(c, p); }
+    int alloc(size_t bytes) { return dev_alloc(c, &p, bytes); }
     double *d() { return (double *)p; }
 };
 
@@ -119,7 +121,7 @@ extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t n
         PLSB_ARG(tloc[i] >= 0 && tloc[i] < ds->N, "test index %lld out of range", (long long)tloc[i]);
     const int64_t rows_local = nfolds_local * ts, rows_total = nfolds_total * ts;
 
-    CvBuf G, S0, idx, Ed, S, P, R, w, Gr, U;
+    CvBuf G(c), S0(c), idx(c), Ed(c), S(c), P(c), R(c), w(c), Gr(c), U(c);
     const int64_t ldg = round_up(K, 2);
     PLSB_TRY(G.alloc((size_t)K * ldg * 8));
     PLSB_CUDA(cudaMemsetAsync(G.p, 0, (size_t)K * ldg * 8, c->stream));
@@ -131,8 +133,8 @@ extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t n
     PLSB_TRY(Ed.alloc((size_t)M * A * rows_local * 8));
 
     // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles
-    size_t free_b = 0, total_b = 0;
-    PLSB_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    size_t free_b = 0;
+    PLSB_TRY(dev_mem_available(c, &free_b));
     const size_t per_fold = (size_t)(M + 2 * A + 2) * ldk * 8 + (size_t)ts * 8;
     int64_t F = (int64_t)((double)free_b * 0.6 / (double)per_fold);
     if (F > 4096) F = 4096;

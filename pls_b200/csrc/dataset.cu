@@ -15,7 +15,7 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
     if (kc < 1) kc = 1;
     if (kc > cols) kc = cols;
     double *stage = nullptr;
-    PLSB_CUDA(cudaMalloc(&stage, (size_t)rows * kc * sizeof(double)));
+    PLSB_TRY(dev_alloc(c, (void **)&stage, (size_t)rows * kc * sizeof(double)));
     int rc = PLSB_OK;
     for (int64_t c0 = 0; c0 < cols && rc == PLSB_OK; c0 += kc) {
         const int64_t nc = cols - c0 < kc ? cols - c0 : kc;
@@ -26,7 +26,7 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
     }
     cudaError_t e = cudaStreamSynchronize(c->stream);
     if (rc == PLSB_OK && e != cudaSuccess) rc = cuda_fail(e, "upload sync", __FILE__, __LINE__);
-    cudaFree(stage);
+    dev_free(c, stage);
     return rc;
 }
 
@@ -39,13 +39,13 @@ static int dataset_alloc(plsb_ctx *c, int64_t N, int64_t K, int64_t M, plsb_data
     ds->ldk = round_up(K, 2);
     ds->ldm = round_up(M, 2);
     const size_t nx = (size_t)(N > 0 ? N : 1) * ds->ldk, ny = (size_t)(N > 0 ? N : 1) * ds->ldm;
-    cudaError_t e = cudaMalloc(&ds->X, nx * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&ds->Y, ny * sizeof(double));
+    cudaError_t e = cudaMallocAsync(&ds->X, nx * sizeof(double), c->stream);
+    if (e == cudaSuccess) e = cudaMallocAsync(&ds->Y, ny * sizeof(double), c->stream);
     if (e == cudaSuccess && ds->ldk != K) e = cudaMemsetAsync(ds->X, 0, nx * sizeof(double), c->stream);
     if (e == cudaSuccess && ds->ldm != M) e = cudaMemsetAsync(ds->Y, 0, ny * sizeof(double), c->stream);
     if (e != cudaSuccess) {
-        if (ds->X) cudaFree(ds->X);
-        if (ds->Y) cudaFree(ds->Y);
+        dev_free(c, ds->X);
+        dev_free(c, ds->Y);
         delete ds;
         return cuda_fail(e, "dataset alloc", __FILE__, __LINE__);
     }
@@ -101,8 +101,8 @@ int plsb_dataset_destroy(plsb_dataset_t ds) {
     if (!ds) return PLSB_OK;
     cudaSetDevice(ds->ctx->device);
     cudaStreamSynchronize(ds->ctx->stream);
-    if (ds->X) cudaFree(ds->X);
-    if (ds->Y) cudaFree(ds->Y);
+    dev_free(ds->ctx, ds->X);
+    dev_free(ds->ctx, ds->Y);
     delete ds;
     return PLSB_OK;
 }
@@ -126,7 +126,7 @@ static int download_rm_to_cm(plsb_ctx *c, const double *src, int64_t lds, int64_
     if (kc < 1) kc = 1;
     if (kc > cols) kc = cols;
     double *stage = nullptr;
-    PLSB_CUDA(cudaMalloc(&stage, (size_t)rows * kc * sizeof(double)));
+    PLSB_TRY(dev_alloc(c, (void **)&stage, (size_t)rows * kc * sizeof(double)));
     int rc = PLSB_OK;
     for (int64_t c0 = 0; c0 < cols && rc == PLSB_OK; c0 += kc) {
         const int64_t nc = cols - c0 < kc ? cols - c0 : kc;
@@ -137,7 +137,7 @@ static int download_rm_to_cm(plsb_ctx *c, const double *src, int64_t lds, int64_
         if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
         if (e != cudaSuccess) rc = cuda_fail(e, "cudaMemcpy2DAsync(D2H)", __FILE__, __LINE__);
     }
-    cudaFree(stage);
+    dev_free(c, stage);
     return rc;
 }
 

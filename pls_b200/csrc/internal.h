@@ -38,6 +38,13 @@ struct plsb_dataset {
 namespace plsb {
 
 int ensure_part(plsb_ctx *c, size_t bytes);
+// Stream-ordered allocations from the device's default memory pool.  plsb_ctx_create raises the pool's release
+// threshold so freed blocks stay cached: repeated fits / CV calls / uploads do not pay cudaMalloc again
+// (multi-GB cudaMalloc + cudaFree cost tens of ms per call).  plsb_ctx_trim returns the cache to the driver.
+int dev_alloc(plsb_ctx *c, void **p, size_t bytes);
+void dev_free(plsb_ctx *c, void *p);
+// free device memory as the wave sizing should see it: driver-free plus what the pool holds unused
+int dev_mem_available(plsb_ctx *c, size_t *bytes);
 // in-place sum across the communicator's ranks on c->stream (no-op without a communicator)
 int allreduce_sum(plsb_ctx *c, double *buf, size_t n);
 // upload a host column-major matrix into a device row-major one (staged, chunked by columns)

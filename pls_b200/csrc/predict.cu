@@ -104,9 +104,11 @@ __global__ void __launch_bounds__(256) colsumsq_kernel(const double *__restrict_
 }
 
 struct Tmp {
+    plsb_ctx *c;
     double *p = nullptr;
-    ~Tmp() { if (p) cudaFree(p); }
-    int alloc(size_t n) { PLSB_CUDA(cudaMalloc(&p, (n ? n : 1) * sizeof(double))); return PLSB_OK; }
+    explicit Tmp(plsb_ctx *ctx) : c(ctx) {}
+    ~Tmp() { dev_free(c, p); }
+    int alloc(size_t n) { return dev_alloc(c, (void **)&p, (n ? n : 1) * sizeof(double)); }
 };
 
 // upload Xn (row-major, padded) and the first `comp` columns of R; compute S (comp x Nn on device)
@@ -143,7 +145,7 @@ static int predict_common(plsb_ctx *c, const double *R, const double *Q, int64_t
         if (want_sse) for (int64_t i = 0; i < M * (mode == 0 ? A : 1); ++i) out[i] = 0.0;
         return PLSB_OK;
     }
-    Tmp Xd, Rd, Sd, Qd, Yd, Od;
+    Tmp Xd(c), Rd(c), Sd(c), Qd(c), Yd(c), Od(c);
     PLSB_TRY(scores_device(c, R, K, comp, Xn, ldx, Nn, Xd, Rd, Sd));
     const int64_t ldm = round_up(M, 2);
     PLSB_TRY(Qd.alloc((size_t)comp * M));
@@ -161,7 +163,7 @@ static int predict_common(plsb_ctx *c, const double *R, const double *Q, int64_t
     PLSB_CUDA(cudaGetLastError());
     if (want_sse) {  // column sums of squares of the residual block: (m, c) -> out[c*M + m]
         const int64_t nc = (mode == 0) ? A : 1;  // component counts per response in the block
-        Tmp Sd2;
+        Tmp Sd2(c);
         PLSB_TRY(Sd2.alloc((size_t)M * nc));
         colsumsq_kernel<<<(unsigned)(M * nc), 256, 0, c->stream>>>(Od.p, Nn, Sd2.p);
         c->launches++;
@@ -190,7 +192,7 @@ int plsb_scores(plsb_ctx_t c, const double *R, int64_t K, int64_t comp, const do
     PLSB_ARG(comp >= 1, "component count must be >= 1");
     PLSB_CUDA(cudaSetDevice(c->device));
     if (Nn == 0) return PLSB_OK;
-    Tmp Xd, Rd, Sd;
+    Tmp Xd(c), Rd(c), Sd(c);
     PLSB_TRY(scores_device(c, R, K, comp, Xn, ldx, Nn, Xd, Rd, Sd));
     PLSB_CUDA(cudaMemcpyAsync(S, Sd.p, (size_t)comp * Nn * 8, cudaMemcpyDeviceToHost, c->stream));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
@@ -222,7 +224,7 @@ int plsb_coefficients(plsb_ctx_t c, const double *R, const double *Q, int64_t K,
     PLSB_ARG(c && R && Q && B, "null argument");
     PLSB_ARG(comp >= 0 && K >= 1 && M >= 1, "bad shape");
     PLSB_CUDA(cudaSetDevice(c->device));
-    Tmp Rd, Qd, Bd;
+    Tmp Rd(c), Qd(c), Bd(c);
     PLSB_TRY(Rd.alloc((size_t)comp * K));
     PLSB_TRY(Qd.alloc((size_t)comp * M));
     PLSB_TRY(Bd.alloc((size_t)K * M));
