@@ -20,6 +20,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 C4 = dict(N=1_000_000, K=2048, M=8, A=32, L=16, seed=20260004)
+C5 = dict(N=20_000, K=4096, M=4, A=64, L=16, seed=20260005)
 WORKLOAD = "C4: synthetic X 1000000x2048, Y x8, FP64, 32 components, KERNEL_TYPE1 single fit"
 
 
@@ -153,6 +154,7 @@ def run_ours(args):
     pass_ms, npass = ctx.profile_get("pass_fused")
     xty_ms, nxty = ctx.profile_get("pass_xty")
     step_ms, nstep = ctx.profile_get("step")
+    red_ms, nred = ctx.profile_get("reduce")
     ctx.profile(False)
     ms_per_step = dev_ms / max(nfit, 1)
     if dist is not None:
@@ -181,7 +183,8 @@ def run_ours(args):
                 "peak": peak, "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({which})", "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_launch": alg_bytes,
                 "avg_launch_ms": pass_avg, "launches_timed": npass,
-                "other_kernels_ms_per_fit": {"xty_pass": xty_ms / max(nfit, 1), "steps": step_ms / max(nfit, 1)}}
+                "other_kernels_ms_per_fit": {"xty_pass": xty_ms / max(nfit, 1), "steps": step_ms / max(nfit, 1),
+                                             "partial_reductions": red_ms / max(nfit, 1)}}
 
     # ---- end to end through the public API with HOST buffers (upload + fit + results back) --------------
     e2e = None
@@ -213,6 +216,50 @@ def run_ours(args):
                "d2h_bytes_per_step": int(8 * (3 * K * A + M * A + rows * A)), "ms_per_step": e2e_s * 1e3,
                "steps": args.e2e_steps, "what": "plsb_dataset_create(pinned host X,Y) + plsb_fit + W,P,R,Q,T to host"}
 
+    # ---- config 5: full leave-one-out CV, 20 000 fits of 20000 x 4096 (A = 64), folds sharded over the ranks -----
+    cv = None
+    if not args.no_cv:
+        if args.no_e2e:
+            ds.close()      # (the e2e leg released the C4 data set itself)
+        ctx.trim()
+        n5, k5, m5, a5 = C5["N"], C5["K"], C5["M"], C5["A"]
+        ds5 = _capi.Dataset(ctx, synth=(C5["seed"], 0, n5, k5, m5, C5["L"]))      # replicated on every rank
+        te = np.arange(n5, dtype=np.int64).reshape(-1, 1)
+        f0, f1 = sharding.fold_shard(n5, rank, world)
+        E = np.zeros((m5, a5, n5))
+        ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=min(256, f1 - f0), out=E)    # warm-up wave
+        ctx.profile(True); ctx.profile_reset()
+        barrier()
+        t0 = time.perf_counter()
+        ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)              # includes D2H of the residual block
+        barrier()
+        cv_s = time.perf_counter() - t0
+        gemm_ms, ngemm = ctx.profile_get("cv_gemm"); fold_ms, _ = ctx.profile_get("cv_fold"); xtx_ms, _ = ctx.profile_get("xtx")
+        ctx.profile(False)
+        if dist is not None:
+            t = torch.tensor([cv_s], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            cv_s = t.item()
+        gemm_flops = 2.0 * k5 * k5 * a5 * (f1 - f0)
+        fp64_peak = None
+        try:    # calibration only (never on the product path): cuBLAS DGEMM 8192^3 as the FP64 tensor denominator
+            a = torch.randn(8192, 8192, device="cuda", dtype=torch.float64); b = torch.randn_like(a)
+            torch.matmul(a, b); torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(); torch.matmul(a, b); e1.record(); torch.cuda.synchronize()
+            fp64_peak = 2 * 8192 ** 3 / (e0.elapsed_time(e1) * 1e-3) / 1e12
+            del a, b
+        except Exception:
+            pass
+        gemm_tf = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
+        cv = {"workload": "C5: synthetic X 20000x4096, Y x4, FP64, 64 components, full LOO-CV (20000 fits), folds sharded",
+              "fits_per_s": n5 / cv_s, "seconds": cv_s, "folds": n5, "folds_this_rank": f1 - f0,
+              "kernels_ms_rank0": {"dmma_gemm": gemm_ms, "fold_kernels": fold_ms, "xtx": xtx_ms},
+              "gemm_roofline": {"bound": "tensor", "achieved": gemm_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+                                "frac": (gemm_tf / fp64_peak) if (gemm_tf and fp64_peak) else None,
+                                "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, measured in this run (calibration only)"}}
+        ds5.close()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
@@ -229,7 +276,7 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "parallelism": f"rows sharded over {world} rank(s)",
                            "l2": "inputs (16.4 GB of X per fit pass) are larger than L2; no flush needed"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cv": cv, "gpu_launches": int(launches), "clocks": clocks,
                 "device_ms_per_step": dev_ms / max(nfit, 1)}
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -247,6 +294,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-cv", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
