@@ -17,9 +17,10 @@ struct NcclApi {
     int (*CommInitRank)(void **, int, plsb_nccl_uid, int) = nullptr;
     int (*CommDestroy)(void *) = nullptr;
     int (*AllReduce)(const void *, void *, size_t, int, int, void *, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, void *, cudaStream_t) = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
 } g_nccl;
-const int kNcclDouble = 8, kNcclSum = 0;  // ncclFloat64, ncclSum (nccl.h enum values, stable since 2.0)
+const int kNcclDouble = 8, kNcclSum = 0, kNcclInt8 = 0;  // ncclFloat64, ncclSum (nccl.h enum values, stable since 2.0)
 
 int nccl_load() {
     if (g_nccl.h) return PLSB_OK;
@@ -33,6 +34,7 @@ int nccl_load() {
     g_nccl.CommInitRank = (int (*)(void **, int, plsb_nccl_uid, int))dlsym(g_nccl.h, "ncclCommInitRank");
     g_nccl.CommDestroy = (int (*)(void *))dlsym(g_nccl.h, "ncclCommDestroy");
     g_nccl.AllReduce = (int (*)(const void *, void *, size_t, int, int, void *, cudaStream_t))dlsym(g_nccl.h, "ncclAllReduce");
+    g_nccl.AllGather = (int (*)(const void *, void *, size_t, int, void *, cudaStream_t))dlsym(g_nccl.h, "ncclAllGather");
     g_nccl.GetErrorString = (const char *(*)(int))dlsym(g_nccl.h, "ncclGetErrorString");
     if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce) {
         plsb::set_error("NCCL symbols missing");
@@ -45,6 +47,24 @@ int nccl_fail(int rc, const char *what) {
     return PLSB_ERR_NCCL;
 }
 thread_local char g_err[1024] = "";
+
+// host-to-host all-gather of `bytes` per rank through the communicator (set-up traffic only)
+int host_allgather(plsb_ctx *c, const void *mine, void *all, size_t bytes) {
+    if (!g_nccl.AllGather) { plsb::set_error("ncclAllGather missing"); return PLSB_ERR_NCCL; }
+    char *d = nullptr;
+    PLSB_CUDA(cudaMalloc(&d, bytes * (size_t)(c->nranks + 1)));
+    int rc = PLSB_OK;
+    cudaError_t e = cudaMemcpyAsync(d, mine, bytes, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        int n = g_nccl.AllGather(d, d + bytes, bytes, kNcclInt8, c->comm, c->stream);
+        if (n) rc = nccl_fail(n, "ncclAllGather");
+    }
+    if (rc == PLSB_OK && e == cudaSuccess) e = cudaMemcpyAsync(all, d + bytes, bytes * (size_t)c->nranks, cudaMemcpyDeviceToHost, c->stream);
+    if (rc == PLSB_OK && e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d);
+    if (rc == PLSB_OK && e != cudaSuccess) rc = plsb::cuda_fail(e, "host_allgather", __FILE__, __LINE__);
+    return rc;
+}
 }  // namespace
 
 namespace plsb {
@@ -172,6 +192,7 @@ int plsb_ctx_destroy(plsb_ctx_t c) {
     if (!c) return PLSB_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    xchg_teardown(c);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     for (auto e : c->pool) cudaEventDestroy(e);
@@ -220,6 +241,8 @@ int plsb_comm_init(plsb_ctx_t c, int rank, int nranks, const void *id128) {
     if (rc) return nccl_fail(rc, "ncclCommInitRank");
     c->rank = rank;
     c->nranks = nranks;
+    // peer-memory exchange area for the in-kernel all-reduce (falls back to NCCL per call if it cannot be set up)
+    PLSB_TRY(xchg_setup(c, host_allgather));
     return PLSB_OK;
 }
 

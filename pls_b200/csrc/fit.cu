@@ -47,8 +47,8 @@ int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, 
     for (int64_t a = 0; a < A; ++a) {
         const double *r = Rd + a * ldk;
         if (method == PLSB_KERNEL_TYPE1) {
-            PLSB_TRY(launch_fused_pass(c, ds, r, g.p, Td ? Td + a * ds->N : nullptr));
-            if (shard) PLSB_TRY(allreduce_sum(c, g.p, (size_t)ldk + 1));
+            // one read of this rank's rows; [g | tt] comes back summed over the CTAs AND over the ranks
+            PLSB_TRY(launch_fused_pass(c, ds, r, g.p, Td ? Td + a * ds->N : nullptr, shard));
         } else {
             PLSB_TRY(launch_symv(c, G.p, ldg, (int)K, r, g.p, (int)ldk));
         }
@@ -86,6 +86,7 @@ int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, dou
     if (Q) PLSB_CUDA(cudaMemcpyAsync(Q, Qd.p, (size_t)A * M * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     if (wantT) PLSB_CUDA(cudaMemcpyAsync(T, Td.p, (size_t)A * N * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    if (ds->sharded) PLSB_TRY(xchg_check(c));
     return PLSB_OK;
 }
 

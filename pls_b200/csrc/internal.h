@@ -4,6 +4,9 @@
 
 #include "common.cuh"
 
+#define PLSB_MAX_RANKS 16
+#define PLSB_XCHG_LEN 8192          /* doubles per exchange slot */
+
 struct plsb_ctx {
     int device = 0;
     int sm_count = 148;
@@ -15,6 +18,14 @@ struct plsb_ctx {
     // communicator (lazy-loaded NCCL); rank/nranks == 0/1 when absent
     void *comm = nullptr;
     int rank = 0, nranks = 1;
+    // peer-memory exchange area for the in-kernel all-reduce of the per-component [g | tt] vector (allreduce.cu)
+    struct Xchg {
+        bool ready = false;
+        char *base = nullptr;           // this rank's area (cudaMalloc: IPC-exportable)
+        char *peer[PLSB_MAX_RANKS] = {nullptr};
+        bool ipc_opened[PLSB_MAX_RANKS] = {false};
+        unsigned long long seq = 0;     // exchanges done so far (identical on every rank)
+    } xchg;
     // profiling
     bool prof = false;
     struct Pending { int slot; cudaEvent_t a, b; };
@@ -47,6 +58,14 @@ void dev_free(plsb_ctx *c, void *p);
 int dev_mem_available(plsb_ctx *c, size_t *bytes);
 // in-place sum across the communicator's ranks on c->stream (no-op without a communicator)
 int allreduce_sum(plsb_ctx *c, double *buf, size_t n);
+// out[i] = sum over ranks of (sum_b part[b*ld + i]): the cross-CTA partial-row sum of a pass fused with the
+// cross-GPU all-reduce over NVLink peer memory when `across_ranks` (falls back to the sum kernel + NCCL when the
+// exchange area is not available).  nb may be 0 (empty shard).
+int launch_reduce_partials(plsb_ctx *c, const double *part, int64_t ld, int nb, int64_t len, double *out,
+                           bool across_ranks);
+int xchg_setup(plsb_ctx *c, int (*allgather)(plsb_ctx *, const void *, void *, size_t));
+void xchg_teardown(plsb_ctx *c);
+int xchg_check(plsb_ctx *c);  // error if an exchange timed out
 // upload a host column-major matrix into a device row-major one (staged, chunked by columns)
 int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst, int64_t ldd,
                     bool src_on_device);
@@ -69,7 +88,8 @@ int launch_rm_to_cm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
 
 // ---- streaming passes over X (pass.cu) --------------------------------------------------------
 // out[0..ldk) = X'(X r), out[ldk] = t't, t_out[i] = (X r)_i (optional).  One read of X.
-int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out);
+int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out,
+                      bool across_ranks = false);
 // S[m*ldk + k] = sum_i X[i,k] Y[i,m]   (M x ldk, zero padded)
 int launch_xty_pass(plsb_ctx *c, const plsb_dataset *ds, double *S);
 

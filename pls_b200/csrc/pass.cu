@@ -77,38 +77,7 @@ int launch_rm_to_cm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
     return PLSB_OK;
 }
 
-// ------------------------------------------------------------------------------------------------
-// deterministic cross-CTA reduction: out[i] = sum_b part[b*ld + i], b = 0..nb-1 in order
-// ------------------------------------------------------------------------------------------------
-// 32 columns x 8 row groups per CTA: row group y sums partial rows y, y+8, .. with eight independent loads in
-// flight, then the eight group sums are added in group order.  (A one-thread-per-column loop over ~300 rows
-// is a chain of L2 round trips: 54 us between two 2.4 ms passes; this shape takes a few us.)
-__global__ void __launch_bounds__(256) reduce_partials_kernel(const double *__restrict__ part, int64_t ld, int nb,
-                                                              int64_t len, double *__restrict__ out) {
-    __shared__ double sm[8][33];
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    const int64_t i = (int64_t)blockIdx.x * 32 + tx;
-    double acc = 0.0;
-    if (i < len) {
-        const double *p = part + i;
-        int b = ty;
-        for (; b + 56 < nb; b += 64) {
-            const double v0 = p[(int64_t)b * ld], v1 = p[(int64_t)(b + 8) * ld], v2 = p[(int64_t)(b + 16) * ld],
-                         v3 = p[(int64_t)(b + 24) * ld], v4 = p[(int64_t)(b + 32) * ld], v5 = p[(int64_t)(b + 40) * ld],
-                         v6 = p[(int64_t)(b + 48) * ld], v7 = p[(int64_t)(b + 56) * ld];
-            acc += ((v0 + v1) + (v2 + v3)) + ((v4 + v5) + (v6 + v7));
-        }
-        for (; b < nb; b += 8) acc += p[(int64_t)b * ld];
-    }
-    sm[ty][tx] = acc;
-    __syncthreads();
-    if (ty == 0 && i < len) {
-        double t = 0.0;
-#pragma unroll
-        for (int y = 0; y < 8; ++y) t += sm[y][tx];
-        out[i] = t;
-    }
-}
+// (the deterministic cross-CTA sum of the per-CTA partial rows lives in allreduce.cu: launch_reduce_partials)
 
 // ------------------------------------------------------------------------------------------------
 // the pass kernels
@@ -397,7 +366,7 @@ static int env_int(const char *name, int dflt) {
 }
 
 template <int NT, int TPR, int VEC, int RB>
-static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out) {
+static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
     using C = PassCfg<NT, TPR, VEC, RB>;
     PassArgs a{};
     a.X = ds->X; a.r = r; a.t_out = t_out; a.N = ds->N; a.ldk = (int)ds->ldk; a.ldp = (int)ds->ldk + 2;
@@ -431,35 +400,27 @@ static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, doubl
         kern<<<(unsigned)grid, NT, smem, c->stream>>>(a);
     }
     PLSB_CUDA(cudaGetLastError());
-    {
-        ProfScope ps(c, PLSB_PROF_REDUCE);
-        reduce_partials_kernel<<<(unsigned)ceil_div(a.ldk + 1, 32), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid,
-                                                                                          a.ldk + 1, out);
-    }
-    PLSB_CUDA(cudaGetLastError());
-    c->launches += 2;
-    return PLSB_OK;
+    c->launches += 1;
+    return launch_reduce_partials(c, c->part, a.ldp, (int)grid, a.ldk + 1, out, across_ranks);
 }
 
-int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out) {
+int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
     const int64_t ldk = ds->ldk;
-    if (ds->N == 0) {  // empty shard: zero contribution
-        PLSB_CUDA(cudaMemsetAsync(out, 0, (size_t)(ldk + 1) * sizeof(double), c->stream));
-        return PLSB_OK;
-    }
+    if (ds->N == 0)  // empty shard: zero contribution, but it still takes part in the exchange
+        return launch_reduce_partials(c, out, ldk + 2, 0, ldk + 1, out, across_ranks);
     const int rbsel = env_int("PLSB_PASS_RB", 0);
-    if (ldk <= 64) return run_fused<256, 32, 2, 8>(c, ds, r, out, t_out);
-    if (ldk <= 128) return run_fused<256, 32, 4, 4>(c, ds, r, out, t_out);
-    if (ldk <= 256) return run_fused<256, 32, 8, 2>(c, ds, r, out, t_out);
-    if (ldk <= 512) return run_fused<256, 256, 2, 8>(c, ds, r, out, t_out);
-    if (ldk <= 1024) return run_fused<256, 256, 4, 4>(c, ds, r, out, t_out);
+    if (ldk <= 64) return run_fused<256, 32, 2, 8>(c, ds, r, out, t_out, across_ranks);
+    if (ldk <= 128) return run_fused<256, 32, 4, 4>(c, ds, r, out, t_out, across_ranks);
+    if (ldk <= 256) return run_fused<256, 32, 8, 2>(c, ds, r, out, t_out, across_ranks);
+    if (ldk <= 512) return run_fused<256, 256, 2, 8>(c, ds, r, out, t_out, across_ranks);
+    if (ldk <= 1024) return run_fused<256, 256, 4, 4>(c, ds, r, out, t_out, across_ranks);
     if (ldk <= 2048) {  // 4 rows per thread and tile: 3-6 % faster than 2 on B200 (fewer barriers per byte)
-        if (rbsel == 2) return run_fused<256, 256, 8, 2>(c, ds, r, out, t_out);
-        return run_fused<256, 256, 8, 4>(c, ds, r, out, t_out);
+        if (rbsel == 2) return run_fused<256, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
+        return run_fused<256, 256, 8, 4>(c, ds, r, out, t_out, across_ranks);
     }
     if (ldk <= 4096) {
-        if (rbsel == 4) return run_fused<512, 512, 8, 4>(c, ds, r, out, t_out);
-        return run_fused<512, 512, 8, 2>(c, ds, r, out, t_out);
+        if (rbsel == 4) return run_fused<512, 512, 8, 4>(c, ds, r, out, t_out, across_ranks);
+        return run_fused<512, 512, 8, 2>(c, ds, r, out, t_out, across_ranks);
     }
     set_error("fused pass: K=%lld > 4096 is not supported yet", (long long)ds->K);
     return PLSB_ERR_UNSUPPORTED;
@@ -504,10 +465,8 @@ static int run_xty(plsb_ctx *c, const plsb_dataset *ds, double *S) {
         }
         PLSB_CUDA(cudaGetLastError());
         const int64_t len = (int64_t)a.mc * a.ldk;
-        reduce_partials_kernel<<<(unsigned)ceil_div(len, 32), 256, 0, c->stream>>>(c->part, a.ldp, (int)grid, len,
-                                                                                     S + (size_t)m0 * a.ldk);
-        PLSB_CUDA(cudaGetLastError());
-        c->launches += 2;
+        c->launches += 1;
+        PLSB_TRY(launch_reduce_partials(c, c->part, a.ldp, (int)grid, len, S + (size_t)m0 * a.ldk, false));
     }
     return PLSB_OK;
 }
