@@ -365,6 +365,111 @@ static int env_int(const char *name, int dflt) {
     return (v && *v) ? atoi(v) : dflt;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Wide matrices (K > 4096): a row tile no longer fits the shared-memory ring, so the component pass falls back
+// to two plain streaming kernels — t = X r, then [g | tt] = [X't | t't] — and X'Y to the second one with Y's
+// columns in the role of t.  Two reads of X per component (what the reference does, pls.cpp:419-421); every
+// element is still read with coalesced 128-bit loads and summed without atomics.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) wide_xr_kernel(const double *__restrict__ X, int64_t N, int ldk,
+                                                      const double *__restrict__ r, double *__restrict__ t) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int64_t row = (int64_t)blockIdx.x * 8 + warp; row < N; row += (int64_t)gridDim.x * 8) {
+        const double2 *x = reinterpret_cast<const double2 *>(X + row * ldk);
+        const double2 *rr = reinterpret_cast<const double2 *>(r);
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int k = lane;
+        for (; k + 32 < ldk / 2; k += 64) {
+            const double2 a = x[k], b = x[k + 32], ra = rr[k], rb = rr[k + 32];
+            s0 = fma(a.x, ra.x, s0); s1 = fma(a.y, ra.y, s1);
+            s2 = fma(b.x, rb.x, s2); s3 = fma(b.y, rb.y, s3);
+        }
+        for (; k < ldk / 2; k += 32) {
+            const double2 a = x[k], ra = rr[k];
+            s0 = fma(a.x, ra.x, s0); s1 = fma(a.y, ra.y, s1);
+        }
+        const double s = warp_sum((s0 + s1) + (s2 + s3));
+        if (lane == 0) t[row] = s;
+    }
+}
+
+// part[cta][v*ldk + k] = sum over the CTA's rows of X[i][k] * V[i*ldv + v0 + v], v < nv <= NV;
+// with_tt: part[cta][ldk] = sum of V[i*ldv]^2 over the same rows (nv == 1)
+template <int NV>
+__global__ void __launch_bounds__(256) wide_xtv_kernel(const double *__restrict__ X, int64_t N, int ldk,
+                                                       const double *__restrict__ V, int ldv, int v0, int nv,
+                                                       double *__restrict__ part, int64_t ldp, int with_tt) {
+    const int64_t rows_per = (N + gridDim.x - 1) / gridDim.x;
+    const int64_t r0 = (int64_t)blockIdx.x * rows_per, r1 = r0 + rows_per < N ? r0 + rows_per : N;
+    double *prow = part + (size_t)blockIdx.x * ldp;
+    for (int c0 = 2 * (int)threadIdx.x; c0 < ldk; c0 += 512) {
+        double a0[NV], a1[NV];
+#pragma unroll
+        for (int v = 0; v < NV; ++v) { a0[v] = 0.0; a1[v] = 0.0; }
+        for (int64_t i = r0; i < r1; ++i) {
+            const double2 x = *reinterpret_cast<const double2 *>(X + i * ldk + c0);
+#pragma unroll
+            for (int v = 0; v < NV; ++v) {
+                const double y = v < nv ? V[i * ldv + v0 + v] : 0.0;
+                a0[v] = fma(x.x, y, a0[v]);
+                a1[v] = fma(x.y, y, a1[v]);
+            }
+        }
+#pragma unroll
+        for (int v = 0; v < NV; ++v)
+            if (v < nv) { prow[(size_t)v * ldk + c0] = a0[v]; prow[(size_t)v * ldk + c0 + 1] = a1[v]; }
+    }
+    if (with_tt) {
+        __shared__ double red[8];
+        double acc = 0.0;
+        for (int64_t i = r0 + threadIdx.x; i < r1; i += 256) acc = fma(V[i * ldv], V[i * ldv], acc);
+        acc = warp_sum(acc);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double tt = 0.0;
+            for (int w = 0; w < 8; ++w) tt += red[w];
+            prow[ldk] = tt;
+        }
+    }
+}
+
+static int run_wide_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
+    const int ldk = (int)ds->ldk;
+    double *t = t_out;
+    if (!t) PLSB_TRY(dev_alloc(c, (void **)&t, (size_t)ds->N * sizeof(double)));
+    const int64_t grid = (int64_t)c->sm_count * 8;
+    const int64_t ldp = ldk + 2;
+    PLSB_TRY(ensure_part(c, (size_t)grid * ldp * sizeof(double)));
+    {
+        ProfScope ps(c, PLSB_PROF_PASS_FUSED);
+        wide_xr_kernel<<<(unsigned)grid, 256, 0, c->stream>>>(ds->X, ds->N, ldk, r, t);
+        wide_xtv_kernel<1><<<(unsigned)grid, 256, 0, c->stream>>>(ds->X, ds->N, ldk, t, 1, 0, 1, c->part, ldp, 1);
+    }
+    PLSB_CUDA(cudaGetLastError());
+    c->launches += 2;
+    if (!t_out) dev_free(c, t);
+    return launch_reduce_partials(c, c->part, ldp, (int)grid, ldk + 1, out, across_ranks);
+}
+
+static int run_wide_xty(plsb_ctx *c, const plsb_dataset *ds, double *S) {
+    const int ldk = (int)ds->ldk;
+    const int64_t grid = (int64_t)c->sm_count * 8;
+    const int64_t ldp = (int64_t)8 * ldk;
+    PLSB_TRY(ensure_part(c, (size_t)grid * ldp * sizeof(double)));
+    for (int m0 = 0; m0 < ds->M; m0 += 8) {
+        const int mc = (int)(ds->M - m0 < 8 ? ds->M - m0 : 8);
+        {
+            ProfScope ps(c, PLSB_PROF_PASS_XTY);
+            wide_xtv_kernel<8><<<(unsigned)grid, 256, 0, c->stream>>>(ds->X, ds->N, ldk, ds->Y, (int)ds->ldm, m0, mc, c->part, ldp, 0);
+        }
+        PLSB_CUDA(cudaGetLastError());
+        c->launches += 1;
+        PLSB_TRY(launch_reduce_partials(c, c->part, ldp, (int)grid, (int64_t)mc * ldk, S + (size_t)m0 * ldk, false));
+    }
+    return PLSB_OK;
+}
+
 template <int NT, int TPR, int VEC, int RB>
 static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
     using C = PassCfg<NT, TPR, VEC, RB>;
@@ -422,8 +527,7 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
         if (rbsel == 4) return run_fused<512, 512, 8, 4>(c, ds, r, out, t_out, across_ranks);
         return run_fused<512, 512, 8, 2>(c, ds, r, out, t_out, across_ranks);
     }
-    set_error("fused pass: K=%lld > 4096 is not supported yet", (long long)ds->K);
-    return PLSB_ERR_UNSUPPORTED;
+    return run_wide_fused(c, ds, r, out, t_out, across_ranks);
 }
 
 template <int NT, int TPR, int VEC, int RB, int MC>
@@ -484,8 +588,7 @@ int launch_xty_pass(plsb_ctx *c, const plsb_dataset *ds, double *S) {
     if (ldk <= 1024) return run_xty<256, 256, 4, 4, 8>(c, ds, S);
     if (ldk <= 2048) return run_xty<256, 256, 8, 2, 8>(c, ds, S);
     if (ldk <= 4096) return run_xty<512, 512, 8, 2, 4>(c, ds, S);
-    set_error("xty pass: K=%lld > 4096 is not supported yet", (long long)ds->K);
-    return PLSB_ERR_UNSUPPORTED;
+    return run_wide_xty(c, ds, S);
 }
 
 }  // namespace plsb
