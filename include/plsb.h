@@ -121,6 +121,18 @@ int plsb_sse(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_
 int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
                   const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E);
 
+/* ---- column statistics and z-scoring on the device: SST (pls.cpp:69-77), colwise_stdev (79-87),
+ * colwise_z_scores (93-111) — the CLI's pre-processing (main.cpp:24-25).  Two-pass formulas like the reference;
+ * a zero-variance column becomes NaN exactly as there. ------------------------------------------------------ */
+/* mean / sst / stdev (each K, any may be NULL) of host column-major X; means_in (K or NULL): use these means */
+int plsb_colstats(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K, const double *means_in,
+                  double *mean, double *sst, double *stdev);
+/* Z = (X - mean) / stdev by column; mean_in/stdev_in both NULL: computed from X (N-1 variance) */
+int plsb_colwise_z_scores(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K, const double *mean_in,
+                          const double *stdev_in, double *Z, int64_t ldz);
+/* standardise a device-resident data set in place (X and Y); outputs (K / M values) may be NULL */
+int plsb_dataset_zscore(plsb_dataset_t ds, double *x_mean, double *x_stdev, double *y_mean, double *y_stdev);
+
 /* ---- host-side validation statistics (stay on the CPU: exact integer results, libstdc++ semantics) -- */
 double plsb_normalcdf(double z);                                        /* pls.cpp:152-160 */
 double plsb_wilcoxon(const double *e1, const double *e2, int64_t n);    /* pls.cpp:190-211 */

@@ -24,7 +24,7 @@ SYMBOLS = [
     "plsb_dataset_shape", "plsb_dataset_download", "plsb_dataset_set_sharded",
     "plsb_fit", "plsb_fit_host", "plsb_xty", "plsb_xtx",
     "plsb_scores", "plsb_fitted", "plsb_predict_residuals", "plsb_coefficients", "plsb_sse_prefixes", "plsb_sse",
-    "plsb_cv_folds",
+    "plsb_cv_folds", "plsb_colstats", "plsb_colwise_z_scores", "plsb_dataset_zscore",
     "plsb_normalcdf", "plsb_wilcoxon", "plsb_validation", "plsb_optimal_num_components", "plsb_lso_folds",
     "plsb_profile_enable", "plsb_profile_reset", "plsb_profile_get", "plsb_launch_count",
 ]
@@ -162,6 +162,11 @@ class Dataset:
         check(lib().plsb_dataset_download(self.h, P(X), i64(max(self.N, 1)), P(Y), i64(max(self.N, 1))))
         return X, Y
 
+    def zscore(self):
+        xm = np.zeros(self.K); xs = np.zeros(self.K); ym = np.zeros(self.M); ys = np.zeros(self.M)
+        check(lib().plsb_dataset_zscore(self.h, P(xm), P(xs), P(ym), P(ys)))
+        return xm, xs, ym, ys
+
     def fit(self, A, method=0, want_T=True):
         K, M, N = self.K, self.M, self.N
         W = np.zeros((K, A), order="F"); Pm = np.zeros((K, A), order="F")
@@ -195,6 +200,23 @@ class Dataset:
         check(lib().plsb_cv_folds(self.h, i64(A), C.c_int(method), i64(ntot), i64(ts), IP(test_idx), i64(fold0),
                                   i64(nloc), P(out)))
         return out.transpose(0, 2, 1)
+
+
+def colstats(ctx, X, means=None):
+    X = F(X); N, K = X.shape
+    mean = np.zeros(K); sst = np.zeros(K); sd = np.zeros(K)
+    mi = None if means is None else np.ascontiguousarray(means, dtype=np.float64)
+    check(lib().plsb_colstats(ctx.h, P(X), i64(max(N, 1)), i64(N), i64(K), P(mi), P(mean), P(sst), P(sd)))
+    return mean, sst, sd
+
+
+def colwise_z_scores(ctx, X, mean=None, stdev=None):
+    X = F(X); N, K = X.shape
+    Z = np.zeros((N, K), order="F")
+    m = None if mean is None else np.ascontiguousarray(mean, dtype=np.float64)
+    s = None if stdev is None else np.ascontiguousarray(stdev, dtype=np.float64)
+    check(lib().plsb_colwise_z_scores(ctx.h, P(X), i64(max(N, 1)), i64(N), i64(K), P(m), P(s), P(Z), i64(max(N, 1))))
+    return Z
 
 
 def fit_host(ctx, X, Y, A, method=0, want_T=True):

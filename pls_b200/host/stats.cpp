@@ -85,44 +85,48 @@ void write_matrix_binary(const std::string &filename, const Mat2D &mat) {
     out.write(reinterpret_cast<const char *>(mat.data()), (std::streamsize)(dims[0] * dims[1] * sizeof(double)));
 }
 
-// ---- column statistics: two-pass formulas as the reference evaluates them -------------------------
+// ---- column statistics: on the device (pls_b200/csrc/stats.cu), two-pass formulas like the reference --------
+namespace {
+inline int64_t ldof(const Mat2D &m) { return m.rows() > 0 ? (int64_t)m.rows() : 1; }
+plsb_ctx_t engine_ctx() { return detail::Engine::get().primary(); }
+}  // namespace
+
 Row SST(const Mat2D &mat, const Row &means) {
     if (mat.rows() < 2) return Row::Zero(mat.cols());
     Row out(mat.cols());
-    for (Eigen::Index c = 0; c < mat.cols(); ++c) {
-        float_type acc = 0;
-        for (Eigen::Index r = 0; r < mat.rows(); ++r) {
-            const float_type d = mat(r, c) - means[c];
-            acc += d * d;
-        }
-        out[c] = acc;
-    }
+    std::lock_guard<std::recursive_mutex> lk(detail::Engine::get().mu);
+    detail::ok(plsb_colstats(engine_ctx(), mat.data(), ldof(mat), mat.rows(), mat.cols(), means.data(), nullptr, out.data(),
+                             nullptr), "plsb_colstats");
     return out;
 }
 
-static Row column_means(const Mat2D &mat) {
-    Row mu(mat.cols());
-    for (Eigen::Index c = 0; c < mat.cols(); ++c) {
-        float_type acc = 0;
-        for (Eigen::Index r = 0; r < mat.rows(); ++r) acc += mat(r, c);
-        mu[c] = acc / static_cast<float_type>(mat.rows());
-    }
-    return mu;
+Row SST(const Mat2D &mat) {
+    if (mat.rows() < 2) return Row::Zero(mat.cols());
+    Row out(mat.cols());
+    std::lock_guard<std::recursive_mutex> lk(detail::Engine::get().mu);
+    detail::ok(plsb_colstats(engine_ctx(), mat.data(), ldof(mat), mat.rows(), mat.cols(), nullptr, nullptr, out.data(), nullptr),
+               "plsb_colstats");
+    return out;
 }
 
-Row SST(const Mat2D &mat) { return SST(mat, column_means(mat)); }
-
 Row colwise_stdev(const Mat2D &mat, const Row &means) {
-    const float_type dof = static_cast<float_type>(mat.rows()) - 1;  // unbiased sample variance
-    Row sd = SST(mat, means);
-    for (Eigen::Index c = 0; c < sd.size(); ++c) sd[c] = std::sqrt(sd[c] / dof);
+    Row sd(mat.cols());
+    std::lock_guard<std::recursive_mutex> lk(detail::Engine::get().mu);
+    detail::ok(plsb_colstats(engine_ctx(), mat.data(), ldof(mat), mat.rows(), mat.cols(), means.data(), nullptr, nullptr,
+                             sd.data()), "plsb_colstats");
     return sd;
 }
 
-Row colwise_stdev(const Mat2D &mat) { return colwise_stdev(mat, column_means(mat)); }
+Row colwise_stdev(const Mat2D &mat) {
+    Row sd(mat.cols());
+    std::lock_guard<std::recursive_mutex> lk(detail::Engine::get().mu);
+    detail::ok(plsb_colstats(engine_ctx(), mat.data(), ldof(mat), mat.rows(), mat.cols(), nullptr, nullptr, nullptr, sd.data()),
+               "plsb_colstats");
+    return sd;
+}
 
 Row z_scores(const Row &obs, const Row &mean, const Row &stdev) {
-    Row z(obs.size());
+    Row z(obs.size());  // one observation: K subtractions and divisions, not worth a launch
     for (Eigen::Index c = 0; c < obs.size(); ++c) z[c] = (obs[c] - mean[c]) / stdev[c];
     return z;
 }
@@ -131,14 +135,18 @@ Mat2D colwise_z_scores(const Mat2D &mat, const Row &mean, const Row &stdev) {
     // Parity note: the reference prepares a zero -> one patched copy of stdev but then
     // divides by the ORIGINAL stdev, so a constant column becomes NaN.  Replicated, not fixed.
     Mat2D z(mat.rows(), mat.cols());
-    for (Eigen::Index c = 0; c < mat.cols(); ++c)
-        for (Eigen::Index r = 0; r < mat.rows(); ++r) z(r, c) = (mat(r, c) - mean[c]) / stdev[c];
+    std::lock_guard<std::recursive_mutex> lk(detail::Engine::get().mu);
+    detail::ok(plsb_colwise_z_scores(engine_ctx(), mat.data(), ldof(mat), mat.rows(), mat.cols(), mean.data(), stdev.data(),
+                                     z.data(), ldof(z)), "plsb_colwise_z_scores");
     return z;
 }
 
 Mat2D colwise_z_scores(const Mat2D &mat) {
-    const Row mu = column_means(mat);
-    return colwise_z_scores(mat, mu, colwise_stdev(mat, mu));
+    Mat2D z(mat.rows(), mat.cols());
+    std::lock_guard<std::recursive_mutex> lk(detail::Engine::get().mu);
+    detail::ok(plsb_colwise_z_scores(engine_ctx(), mat.data(), ldof(mat), mat.rows(), mat.cols(), nullptr, nullptr, z.data(),
+                                     ldof(z)), "plsb_colwise_z_scores");
+    return z;
 }
 
 // ---- rank statistics ----------------------------------------------------------------------------------

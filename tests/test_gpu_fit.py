@@ -143,3 +143,34 @@ def test_argument_errors(ctx):
     with pytest.raises(_capi.PlsbError):
         ds.fit(2, 7)
     ds.close()
+
+
+def test_column_statistics_and_z_scores(ctx):
+    """SST / colwise_stdev / colwise_z_scores on the device (pls.cpp:69-111) against the reference's golden values
+    and numpy's two-pass formulas; the zero-variance NaN of the reference is reproduced."""
+    for name in ("c1_toy", "c2_nir_octane"):
+        g = load_golden(name)
+        mean, sst, sd = _capi.colstats(ctx, g["X_raw"])
+        if "x_sst" in g:
+            assert relerr(sst, g["x_sst"]) <= 1e-12 and relerr(sd, g["x_stdev"]) <= 1e-12
+        assert relerr(_capi.colwise_z_scores(ctx, g["X_raw"]), g["X"]) <= 1e-12
+        assert relerr(_capi.colwise_z_scores(ctx, g["Y_raw"]), g["Y"]) <= 1e-12
+        assert relerr(_capi.colwise_z_scores(ctx, g["X_raw"], mean, sd), g["X"]) <= 1e-12
+    rng = np.random.default_rng(5)
+    for N, K in [(2, 1), (37, 15), (1001, 203), (64, 1025)]:
+        X = rng.standard_normal((N, K)) * rng.uniform(0.1, 10, K) + rng.uniform(-5, 5, K)
+        mean, sst, sd = _capi.colstats(ctx, X)
+        mu = X.mean(axis=0)
+        assert relerr(mean, mu) <= 1e-13
+        assert relerr(sst, ((X - mu) ** 2).sum(axis=0)) <= 1e-12
+        assert relerr(sd, X.std(axis=0, ddof=1)) <= 1e-12
+        assert relerr(_capi.colstats(ctx, X, means=np.zeros(K))[1], (X ** 2).sum(axis=0)) <= 1e-12   # SST(mat, means)
+        ds = _capi.Dataset(ctx, X, X[:, :1])
+        xm, xs, ym, ys = ds.zscore()
+        Z, _ = ds.download()
+        assert relerr(Z, (X - mu) / X.std(axis=0, ddof=1)) <= 1e-12 and relerr(xs, sd) <= 1e-12
+        ds.close()
+    assert np.array_equal(_capi.colstats(ctx, np.ones((1, 3)))[1], np.zeros(3))       # N < 2: zeros (pls.cpp:70-71)
+    Xc = rng.standard_normal((10, 4)); Xc[:, 2] = 3.0
+    Z = _capi.colwise_z_scores(ctx, Xc)
+    assert np.isnan(Z[:, 2]).all() and np.isfinite(Z[:, [0, 1, 3]]).all()
