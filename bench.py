@@ -86,6 +86,25 @@ def cpu_reference_fit(n_sample, steps, warmup):
     return (time.time() - t0) / steps, "port", 1
 
 
+def cpu_reference_cv(n_sample):
+    """The reference's plsr per LOO fold (inner A = 64, the first A components of its own cv_LOO are bit-identical),
+    one fold per host thread over all cores, on the first n_sample rows of the C5 matrix; returns
+    (fits/s scaled to N = 20000, threads, seconds)."""
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import port, ref
+    if not ref.available():
+        return None
+    X, Y = port.synth(C5["seed"], n_sample, C5["K"], C5["M"], L=C5["L"])
+    nthr = os.cpu_count() or 1
+    te = np.arange(nthr, dtype=np.int64).reshape(-1, 1)
+    t0 = time.time()
+    with ThreadPoolExecutor(nthr) as ex:     # ctypes releases the GIL: the folds run concurrently
+        list(ex.map(lambda f: ref.cv_folds(X, Y, C5["A"], 0, te[f:f + 1]), range(nthr)))
+    sec = time.time() - t0
+    return nthr / (sec * C5["N"] / n_sample), nthr, sec
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -259,6 +278,15 @@ def run_ours(args):
                                 "frac": (gemm_tf / fp64_peak) if (gemm_tf and fp64_peak) else None,
                                 "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, measured in this run (calibration only)"}}
         ds5.close()
+        if rank == 0 and world == 1 and not args.no_cpu:
+            try:
+                r = cpu_reference_cv(4000)
+                if r:
+                    cv["cpu_baseline"] = {"value": r[0], "unit": "fits/s", "cores": r[1], "kind": "reference",
+                                          "sample": f"{r[1]} LOO folds, one per host thread, reference plsr (A=64) on the first 4000 "
+                                                    f"rows of the C5 matrix ({r[2]:.1f} s), scaled by N/4000"}
+            except Exception as e:
+                cv["cpu_baseline"] = {"error": repr(e)}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
