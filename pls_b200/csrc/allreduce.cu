@@ -8,14 +8,17 @@
 // here the exchange is a flag write, a flag wait and (ranks-1) x 16 KB of peer loads inside the kernel that is
 // running anyway.  Large one-off reductions (X'Y, X'X) stay on NCCL.
 //
-// Protocol (per exchange number seq = 1, 2, ...; every rank runs the same sequence):
-//   1. every CTA sums its 32 columns over the partial rows and stores them in this rank's slot[seq & 1];
-//   2. the last CTA to finish (device-scope counter) publishes flag = seq with system-scope release;
-//   3. every CTA waits until each peer's flag >= seq (acquire), loads its columns from every peer's slot and adds
-//      them in RANK order, own contribution included at its rank position: all ranks get bit-identical sums, so
-//      the replicated K-sized step stays replicated exactly.
-// Two slots suffice: a rank can start exchange seq+2 only after every peer has published seq+1, which it does
-// after it has finished reading exchange seq.  Flags only grow, so there is no reset race.  A peer that never
+// Protocol (per exchange number seq = 1, 2, ...; every rank runs the same sequence) — a PUSH exchange, so that
+// every wait polls local memory and every remote access is a fire-and-forget store:
+//   1. every CTA sums its 32 columns over the partial rows and stores them into slot[seq & 1][my rank] of EVERY
+//      rank's exchange area (remote stores over NVLink; own area included);
+//   2. the last CTA to finish (device-scope counter) fences system-wide and writes flag[my rank] = seq into every
+//      rank's area;
+//   3. every CTA waits until its LOCAL flags of all ranks are >= seq (one polling thread per rank), then adds the
+//      LOCAL slots in RANK order: all ranks get bit-identical sums, so the replicated K-sized step stays
+//      replicated exactly.
+// Two slot sets suffice: a rank can push exchange seq+2 only after every peer has pushed seq+1 to it, which a peer
+// does after it has finished reading exchange seq.  Flags only grow, so there is no reset race.  A peer that never
 // shows up trips a 10 s timeout and raises an error flag instead of hanging the GPU.
 #include <unistd.h>
 
@@ -23,15 +26,16 @@
 
 namespace plsb {
 
-constexpr size_t XCHG_FLAG_OFF = 0;                                   // uint64 flag
-constexpr size_t XCHG_SLOT_OFF = 256;                                 // two slots of PLSB_XCHG_LEN doubles
-constexpr size_t XCHG_BYTES = XCHG_SLOT_OFF + 2 * PLSB_XCHG_LEN * sizeof(double);
+constexpr size_t XCHG_CTR_OFF = 0;                                    // local arrival counter (u32)
+constexpr size_t XCHG_ERR_OFF = 64;                                   // local error flag (int)
+constexpr size_t XCHG_FLAG_OFF = 128;                                 // u64 flag per source rank
+constexpr size_t XCHG_SLOT_OFF = XCHG_FLAG_OFF + PLSB_MAX_RANKS * 8;  // [2][ranks][PLSB_XCHG_LEN] doubles
+constexpr size_t XCHG_BYTES = XCHG_SLOT_OFF + 2 * (size_t)PLSB_MAX_RANKS * PLSB_XCHG_LEN * sizeof(double);
 
 struct XchgArgs {
     int rank, nranks;
     unsigned long long seq;
-    char *mine;
-    const char *peer[PLSB_MAX_RANKS];
+    char *area[PLSB_MAX_RANKS];   // every rank's exchange area (area[rank] is local)
     unsigned *counter;   // device-scope arrival counter (local)
     int *err;            // local error flag (timeout)
 };
@@ -41,8 +45,8 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
     asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
-    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+__device__ __forceinline__ void st_relaxed_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 __device__ __forceinline__ double ld_relaxed_sys(const double *p) {
     double v;
@@ -86,35 +90,41 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double *__re
     }
     if (!ACROSS) return;
 
-    double *slot = reinterpret_cast<double *>(x.mine + XCHG_SLOT_OFF) + (x.seq & 1) * PLSB_XCHG_LEN;
-    if (ty == 0 && i < len) slot[i] = mine;
+    const size_t set = (size_t)(x.seq & 1) * PLSB_MAX_RANKS * PLSB_XCHG_LEN;
+    if (ty == 0 && i < len) {
+#pragma unroll
+        for (int r = 0; r < PLSB_MAX_RANKS; ++r)
+            if (r < x.nranks)
+                reinterpret_cast<double *>(x.area[r] + XCHG_SLOT_OFF)[set + (size_t)x.rank * PLSB_XCHG_LEN + i] = mine;
+    }
     __threadfence_system();
     __syncthreads();
+    char *local = x.area[x.rank];
     if (threadIdx.x == 0) {
         const unsigned prev = atomicAdd(x.counter, 1u);
-        if (prev == gridDim.x - 1) {   // this rank's vector is complete: publish it
+        if (prev == gridDim.x - 1) {   // this rank's vector has been pushed everywhere: announce it
             *x.counter = 0;
             __threadfence_system();
-            st_release_sys(reinterpret_cast<unsigned long long *>(x.mine + XCHG_FLAG_OFF), x.seq);
+            for (int r = 0; r < x.nranks; ++r)
+                st_relaxed_sys(reinterpret_cast<unsigned long long *>(x.area[r] + XCHG_FLAG_OFF) + x.rank, x.seq);
         }
+    }
+    if ((int)threadIdx.x < x.nranks) {   // one polling thread per source rank, all on local memory
+        const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(local + XCHG_FLAG_OFF) + threadIdx.x;
         const unsigned long long t0 = global_ns();
-        for (int r = 0; r < x.nranks; ++r) {
-            if (r == x.rank) continue;
-            const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(x.peer[r] + XCHG_FLAG_OFF);
-            while (ld_acquire_sys(flag) < x.seq) {
-                if (global_ns() - t0 > 10000000000ull) { *x.err = 1; break; }
-            }
+        while (ld_acquire_sys(flag) < x.seq) {
+            if (global_ns() - t0 > 10000000000ull) { *x.err = 1; break; }
         }
     }
     __syncthreads();
     if (ty == 0 && i < len) {
+        const double *slots = reinterpret_cast<const double *>(local + XCHG_SLOT_OFF) + set + i;
+        double v[PLSB_MAX_RANKS];
+#pragma unroll
+        for (int r = 0; r < PLSB_MAX_RANKS; ++r) v[r] = r < x.nranks ? ld_relaxed_sys(slots + (size_t)r * PLSB_XCHG_LEN) : 0.0;
         double tot = 0.0;
-        for (int r = 0; r < x.nranks; ++r) {
-            double v = mine;
-            if (r != x.rank)
-                v = ld_relaxed_sys(reinterpret_cast<const double *>(x.peer[r] + XCHG_SLOT_OFF) + (x.seq & 1) * PLSB_XCHG_LEN + i);
-            tot += v;
-        }
+#pragma unroll
+        for (int r = 0; r < PLSB_MAX_RANKS; ++r) tot += v[r];   // rank order; absent ranks add an exact zero
         out[i] = tot;
     }
 }
@@ -125,10 +135,10 @@ int launch_reduce_partials(plsb_ctx *c, const double *part, int64_t ld, int nb, 
     XchgArgs x{};
     const bool fused = across_ranks && c->nranks > 1 && c->xchg.ready && len <= PLSB_XCHG_LEN && grid <= (unsigned)c->sm_count;
     if (fused) {
-        x.rank = c->rank; x.nranks = c->nranks; x.seq = ++c->xchg.seq; x.mine = c->xchg.base;
-        for (int r = 0; r < c->nranks; ++r) x.peer[r] = c->xchg.peer[r];
-        x.counter = reinterpret_cast<unsigned *>(c->xchg.base + 64);
-        x.err = reinterpret_cast<int *>(c->xchg.base + 128);
+        x.rank = c->rank; x.nranks = c->nranks; x.seq = ++c->xchg.seq;
+        for (int r = 0; r < c->nranks; ++r) x.area[r] = c->xchg.peer[r];
+        x.counter = reinterpret_cast<unsigned *>(c->xchg.base + XCHG_CTR_OFF);
+        x.err = reinterpret_cast<int *>(c->xchg.base + XCHG_ERR_OFF);
     }
     {
         ProfScope ps(c, PLSB_PROF_REDUCE);
@@ -207,7 +217,7 @@ void xchg_teardown(plsb_ctx *c) {
 int xchg_check(plsb_ctx *c) {
     if (!c->xchg.ready) return PLSB_OK;
     int err = 0;
-    PLSB_CUDA(cudaMemcpy(&err, c->xchg.base + 128, sizeof(int), cudaMemcpyDeviceToHost));
+    PLSB_CUDA(cudaMemcpy(&err, c->xchg.base + XCHG_ERR_OFF, sizeof(int), cudaMemcpyDeviceToHost));
     if (err) {
         set_error("peer all-reduce timed out: a rank of the communicator did not reach the exchange");
         return PLSB_ERR_NCCL;
