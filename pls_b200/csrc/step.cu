@@ -38,7 +38,8 @@ __global__ void __launch_bounds__(STEP_NT) step_kernel(const StepArgs s) {
 // warp 0 of every CTA so no broadcast is needed.
 // ------------------------------------------------------------------------------------------------
 namespace cg = cooperative_groups;
-constexpr int SC_NCTA = 8, SC_NT = 256, SC_NW = SC_NT / 32, SC_KPT = 2;  // K <= 8 * 256 * 2 = 4096
+constexpr int SC_NCTA = 8, SC_NT = 256, SC_KPT = 2;  // K <= 8 * 256 * 2 = 4096
+constexpr int SC_CH = 16;  // values reduced per CTA-stage round (staging area: SC_CH x 256 doubles)
 
 struct StepClLay {
     int cpc;      // columns per CTA
@@ -52,7 +53,7 @@ static StepClLay step_cl_layout(int ldk, int M) {
     if (nv < 64) nv = 64;
     l.nvs = (int)round_up(nv, 32);
     const int npairs = M * (M + 1) / 2;
-    l.bytes = sizeof(double) * ((size_t)M * l.cpc + (size_t)SC_NW * l.nvs + (2 * SC_NCTA + 1) * (size_t)l.nvs + (size_t)M * M + 2048 + M + 8) +
+    l.bytes = sizeof(double) * ((size_t)M * l.cpc + (size_t)SC_CH * SC_NT + (2 * SC_NCTA + 1) * (size_t)l.nvs + (size_t)M * M + 2048 + M + 8) +
               (size_t)round_up(2 * npairs, 16);
     return l;
 }
@@ -62,6 +63,7 @@ struct StepClSmem {
     uint64_t *bar;          // two mbarriers (one per exchange parity)
     unsigned char *pu, *pv;
     int nvs, phase, rank;
+    long long *trace;       // dev tool: timestamps inside exchange number 3 (the P'w dots), or null
 };
 
 __device__ __forceinline__ uint32_t cluster_map(const void *smem_ptr, int cta_rank) {
@@ -79,6 +81,11 @@ __device__ __forceinline__ void cluster_barrier() {
     asm volatile("barrier.cluster.arrive.aligned;\n\tbarrier.cluster.wait.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ long long sc_now() {
+    long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 // CTA-level then cluster-level sum of nv per-thread values; the totals land in sm.tot on every CTA.
 // Exchange: every CTA pushes its nv partial sums into a slot of every CTA's `gather` array with st.async; the
 // bytes are counted by the destination's mbarrier, so one wait replaces a cluster-wide barrier (whose release
@@ -87,22 +94,49 @@ __device__ __forceinline__ void cluster_barrier() {
 // CTA has finished reading exchange n (it has sent n+1 since), so two sets suffice.  Sums run in rank order.
 template <typename F>
 __device__ __forceinline__ void cl_reduce(StepClSmem &sm, int nv, F val) {
-    const int tid = threadIdx.x, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const int par = sm.phase & 1;
     uint64_t *bar = sm.bar + par;
     double *gather = sm.gather + (size_t)par * SC_NCTA * sm.nvs;
+    const bool tr = sm.trace != nullptr && sm.phase == 3 && tid == 0 && blockIdx.x == 0;
+    if (tr) sm.trace[11] = sc_now();
     if (tid == 0) mbar_arrive_expect_tx(bar, (uint32_t)(nv * sizeof(double) * SC_NCTA));
-    warp_reduce_many(nv, val, sm.red + (size_t)warp * sm.nvs);
-    __syncthreads();
-    for (int v = tid; v < nv; v += SC_NT) {
-        double t = 0.0;
+    // CTA stage, SC_CH values at a time: every thread parks its partial products in shared memory, then 16 threads
+    // per value add the 256 entries in a fixed order.  Deliberately a small LOOP, not an unrolled register
+    // butterfly: this kernel runs once per component right after a pass has flushed every cache, so each executed
+    // instruction is a cold instruction-cache miss — the unrolled 32-value version (5k instructions) cost 7 us of
+    // pure instruction fetch; this one is a few hundred instructions.
+    const int g = tid >> 4, l = tid & 15;
+    for (int base = 0; base < nv; base += SC_CH) {
+        const int n = nv - base < SC_CH ? nv - base : SC_CH;
+        double pv[SC_CH];
 #pragma unroll
-        for (int w = 0; w < SC_NW; ++w) t += sm.red[(size_t)w * sm.nvs + v];
-        double *slot = gather + (size_t)sm.rank * sm.nvs + v;
+        for (int i = 0; i < SC_CH; ++i) pv[i] = val(base + (i < n ? i : n - 1));   // unconditional: loads stay batched
 #pragma unroll
-        for (int c = 0; c < SC_NCTA; ++c) st_async_f64(cluster_map(slot, c), t, cluster_map(bar, c));
+        for (int i = 0; i < SC_CH; ++i) sm.red[i * SC_NT + tid] = pv[i];
+        __syncthreads();
+        {   // every thread takes part (full-warp shuffles); groups past n re-add the last value and discard it
+            const double *row = sm.red + (g < n ? g : n - 1) * SC_NT + l;
+            double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+            for (int u = 0; u < 16; u += 2) {
+                a0 += row[16 * u];
+                a1 += row[16 * (u + 1)];
+            }
+            double acc = a0 + a1;
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+            if (l == 0 && g < n) {   // this CTA's total of value base+g: push it to every CTA of the cluster
+                double *slot = gather + (size_t)sm.rank * sm.nvs + base + g;
+#pragma unroll
+                for (int c = 0; c < SC_NCTA; ++c) st_async_f64(cluster_map(slot, c), acc, cluster_map(bar, c));
+            }
+        }
+        __syncthreads();
     }
+    if (tr) sm.trace[14] = sc_now();
     mbar_wait(bar, (uint32_t)((sm.phase >> 1) & 1));
+    if (tr) sm.trace[15] = sc_now();
     for (int v = tid; v < nv; v += SC_NT) {
         double t = 0.0;
 #pragma unroll
@@ -113,11 +147,6 @@ __device__ __forceinline__ void cl_reduce(StepClSmem &sm, int nv, F val) {
     sm.phase++;
 }
 
-__device__ __forceinline__ long long sc_now() {
-    long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
 #define SC_TRACE(i) do { if (s.trace && threadIdx.x == 0 && blockIdx.x == 0) s.trace[i] = sc_now(); } while (0)
 __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s, const int cpc, const int nvs) {
     extern __shared__ __align__(16) double sc_smem[];
@@ -126,13 +155,13 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
     const int npairs = M * (M + 1) / 2;
     StepClSmem sm;
     sm.S = sc_smem;                              // M x cpc slice of S
-    sm.red = sm.S + (size_t)M * cpc;             // [warps][nvs]
-    sm.gather = sm.red + (size_t)SC_NW * nvs;    // [2][ctas][nvs] partial sums pushed here by every CTA
+    sm.red = sm.S + (size_t)M * cpc;             // [SC_CH][threads] staging of per-thread partial products
+    sm.gather = sm.red + (size_t)SC_CH * SC_NT;  // [2][ctas][nvs] partial sums pushed here by every CTA
     sm.tot = sm.gather + 2 * (size_t)SC_NCTA * nvs;  // [nvs] cluster totals
     sm.G = sm.tot + nvs; sm.B = sm.G + M * M; sm.C = sm.B + 1024; sm.q = sm.C + 1024;  // B, C: up to 32 x 32 padded
     sm.bar = reinterpret_cast<uint64_t *>(sm.q + M);  // 2 of the 8 spare doubles
     sm.pu = reinterpret_cast<unsigned char *>(sm.q + M + 8); sm.pv = sm.pu + npairs;
-    sm.nvs = nvs; sm.phase = 0;
+    sm.nvs = nvs; sm.phase = 0; sm.trace = s.trace;
     const int tid = threadIdx.x, warp = tid >> 5;
     const int rank = (int)cluster.block_rank();
     sm.rank = rank;
@@ -323,6 +352,8 @@ static int launch_step_cluster(plsb_ctx *c, const StepArgs &s) {
         PLSB_CUDA(cudaStreamSynchronize(c->stream));
         fprintf(stderr, "step a=%d ns:", s.a);
         for (int i = 1; i < 10; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[0] : -1);
+        fprintf(stderr, " | x3:");
+        for (int i = 14; i < 16; ++i) fprintf(stderr, " %lld", h[i] ? h[i] - h[11] : -1);
         fprintf(stderr, " | squarings %lld", h[10]);
         fprintf(stderr, "\n");
         c->launches++;
