@@ -92,6 +92,9 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
                       bool across_ranks = false);
 // S[m*ldk + k] = sum_i X[i,k] Y[i,m]   (M x ldk, zero padded)
 int launch_xty_pass(plsb_ctx *c, const plsb_dataset *ds, double *S);
+// the DMMA + TMA variant (xty.cu); launch_xty_pass routes to it when supported
+bool xty_dmma_supported(const plsb_dataset *ds);
+int launch_xty_dmma(plsb_ctx *c, const plsb_dataset *ds, double *S);
 
 // ---- per-component step (step.cu) -------------------------------------------------------------
 struct StepArgs {

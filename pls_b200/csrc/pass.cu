@@ -581,6 +581,8 @@ int launch_xty_pass(plsb_ctx *c, const plsb_dataset *ds, double *S) {
         PLSB_CUDA(cudaMemsetAsync(S, 0, (size_t)ds->M * ldk * sizeof(double), c->stream));
         return PLSB_OK;
     }
+    // FP64 tensor-core path (xty.cu) for rows of 2-16 KB; PLSB_XTY_FMA=1 keeps the FMA kernels for A/B runs
+    if (xty_dmma_supported(ds) && !env_int("PLSB_XTY_FMA", 0)) return launch_xty_dmma(c, ds, S);
     if (ldk <= 64) return run_xty<256, 32, 2, 8, 8>(c, ds, S);
     if (ldk <= 128) return run_xty<256, 32, 4, 4, 8>(c, ds, S);
     if (ldk <= 256) return run_xty<256, 32, 8, 2, 8>(c, ds, S);

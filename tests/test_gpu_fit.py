@@ -101,6 +101,17 @@ def test_cross_products(ctx):
     ds.close()
 
 
+@pytest.mark.parametrize("N,K,M", [(1003, 700, 11), (5, 256, 1), (4099, 2047, 8), (777, 1024, 16), (3, 1999, 2)])
+def test_xty_dmma_path(ctx, N, K, M):
+    """X'Y (pls.cpp:396) through the DMMA + TMA kernel (xty.cu): ragged row tails, M not a multiple of 8."""
+    X, Y = port.synth(4000 + N, N, K, M)
+    ds = _capi.Dataset(ctx, X, Y)
+    S = ds.xty()
+    assert relerr(S, X.T @ Y) <= 1e-12
+    assert np.array_equal(S, ds.xty())          # reproducible bit for bit
+    ds.close()
+
+
 def test_type1_equals_type2_and_invariants(ctx):
     ds = _capi.Dataset(ctx, synth=(7, 0, 5000, 384, 4, 16))
     a = ds.fit(12, 0); b = ds.fit(12, 1)
