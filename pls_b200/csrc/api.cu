@@ -177,6 +177,9 @@ int plsb_ctx_create(int device, plsb_ctx_t *out) {
     c->sm_count = prop.multiProcessorCount;
     c->smem_optin = prop.sharedMemPerBlockOptin;
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->xfer_ev[i], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->col_ev, cudaEventDisableTiming);
     if (e != cudaSuccess) { delete c; return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__); }
     {   // keep freed blocks in the pool (see dev_alloc)
         cudaMemPool_t pool;
@@ -199,6 +202,9 @@ int plsb_ctx_destroy(plsb_ctx_t c) {
     if (c->part) cudaFreeAsync(c->part, c->stream);
     cudaStreamSynchronize(c->stream);
     cudaStreamDestroy(c->stream);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    for (int i = 0; i < 4; ++i) if (c->xfer_ev[i]) cudaEventDestroy(c->xfer_ev[i]);
+    if (c->col_ev) cudaEventDestroy(c->col_ev);
     delete c;
     return PLSB_OK;
 }

@@ -9,22 +9,37 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
                     bool src_on_device) {
     if (rows == 0 || cols == 0) return PLSB_OK;
     if (src_on_device) return launch_cm_to_rm(c, src, lds, rows, cols, dst, ldd, 0);
-    // stage column blocks of <= 256 MB through one device buffer; the transpose runs at HBM speed,
-    // so the copy engine is the only thing that matters here
-    int64_t kc = (int64_t)(256u << 20) / (rows * 8);
+    // Column blocks of <= 128 MB go through TWO staging buffers: the copy engine fills one (copy_stream) while the
+    // transpose kernel empties the other (stream), so PCIe never waits for a kernel.  The transpose runs at HBM
+    // speed; the copy engine is the only thing that matters here.
+    int64_t kc = (int64_t)(128u << 20) / (rows * 8);
     if (kc < 1) kc = 1;
     if (kc > cols) kc = cols;
     double *stage = nullptr;
-    PLSB_TRY(dev_alloc(c, (void **)&stage, (size_t)rows * kc * sizeof(double)));
+    PLSB_TRY(dev_alloc(c, (void **)&stage, (size_t)2 * rows * kc * sizeof(double)));
+    cudaEvent_t *copied = c->xfer_ev, *moved = c->xfer_ev + 2;
     int rc = PLSB_OK;
-    for (int64_t c0 = 0; c0 < cols && rc == PLSB_OK; c0 += kc) {
+    cudaError_t e = cudaEventRecord(moved[0], c->stream);     // orders the first copies after the allocation
+    if (e == cudaSuccess) e = cudaEventRecord(moved[1], c->stream);
+    int64_t i = 0;
+    for (int64_t c0 = 0; c0 < cols && rc == PLSB_OK && e == cudaSuccess; c0 += kc, ++i) {
         const int64_t nc = cols - c0 < kc ? cols - c0 : kc;
-        cudaError_t e = cudaMemcpy2DAsync(stage, (size_t)rows * 8, src + c0 * lds, (size_t)lds * 8, (size_t)rows * 8,
-                                          (size_t)nc, cudaMemcpyHostToDevice, c->stream);
-        if (e != cudaSuccess) { rc = cuda_fail(e, "cudaMemcpy2DAsync(H2D)", __FILE__, __LINE__); break; }
-        rc = launch_cm_to_rm(c, stage, rows, rows, nc, dst, ldd, c0);
+        const int b = (int)(i & 1);
+        double *buf = stage + (size_t)b * rows * kc;
+        e = cudaStreamWaitEvent(c->copy_stream, moved[b], 0);  // block i-2 has left this buffer
+        if (e == cudaSuccess)
+            e = cudaMemcpy2DAsync(buf, (size_t)rows * 8, src + c0 * lds, (size_t)lds * 8, (size_t)rows * 8, (size_t)nc,
+                                  cudaMemcpyHostToDevice, c->copy_stream);
+        if (e == cudaSuccess) e = cudaEventRecord(copied[b], c->copy_stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, copied[b], 0);
+        if (e != cudaSuccess) break;
+        rc = launch_cm_to_rm(c, buf, rows, rows, nc, dst, ldd, c0);
+        if (rc == PLSB_OK) e = cudaEventRecord(moved[b], c->stream);
     }
-    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess && rc == PLSB_OK) rc = cuda_fail(e, "upload (H2D)", __FILE__, __LINE__);
+    e = cudaStreamSynchronize(c->copy_stream);
+    if (rc == PLSB_OK && e != cudaSuccess) rc = cuda_fail(e, "upload sync", __FILE__, __LINE__);
+    e = cudaStreamSynchronize(c->stream);
     if (rc == PLSB_OK && e != cudaSuccess) rc = cuda_fail(e, "upload sync", __FILE__, __LINE__);
     dev_free(c, stage);
     return rc;

@@ -23,7 +23,10 @@ struct DevBuf {
 int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg);  // gemm.cu
 
 // device-side fit; outputs stay on the device (A x ldk / A x M / A x N, "component-major")
-int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, double *Rd, double *Qd, double *Td) {
+// T_host (optional, PINNED host memory, N x A column-major): column a of the scores is sent home on the copy
+// stream as soon as pass a has produced it, under the following passes, instead of after the fit.
+int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, double *Rd, double *Qd, double *Td,
+               double *T_host = nullptr) {
     plsb_ctx *c = ds->ctx;
     const int64_t K = ds->K, ldk = ds->ldk, M = ds->M;
     const bool shard = ds->sharded && c->nranks > 1;
@@ -49,6 +52,12 @@ int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, 
         if (method == PLSB_KERNEL_TYPE1) {
             // one read of this rank's rows; [g | tt] comes back summed over the CTAs AND over the ranks
             PLSB_TRY(launch_fused_pass(c, ds, r, g.p, Td ? Td + a * ds->N : nullptr, shard));
+            if (Td && T_host) {
+                PLSB_CUDA(cudaEventRecord(c->col_ev, c->stream));
+                PLSB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->col_ev, 0));
+                PLSB_CUDA(cudaMemcpyAsync(T_host + a * ds->N, Td + a * ds->N, (size_t)ds->N * sizeof(double),
+                                          cudaMemcpyDeviceToHost, c->copy_stream));
+            }
         } else {
             PLSB_TRY(launch_symv(c, G.p, ldg, (int)K, r, g.p, (int)ldk));
         }
@@ -78,13 +87,21 @@ int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, dou
     PLSB_TRY(Qd.alloc((size_t)A * M, true));
     const bool wantT = T != nullptr && method == PLSB_KERNEL_TYPE1 && N > 0;
     if (wantT) PLSB_TRY(Td.alloc((size_t)A * N, false));
-    PLSB_TRY(fit_device(ds, A, method, Wd.p, Pd.p, Rd.p, Qd.p, wantT ? Td.p : nullptr));
+    // a pageable destination would make every cudaMemcpyAsync block the launching thread: stream T only to pinned memory
+    bool streamT = false;
+    if (wantT) {
+        cudaPointerAttributes pa{};
+        streamT = cudaPointerGetAttributes(&pa, T) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+    }
+    PLSB_TRY(fit_device(ds, A, method, Wd.p, Pd.p, Rd.p, Qd.p, wantT ? Td.p : nullptr, streamT ? T : nullptr));
     const size_t kb = (size_t)K * sizeof(double), lb = (size_t)ldk * sizeof(double);
     if (W) PLSB_CUDA(cudaMemcpy2DAsync(W, kb, Wd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
     if (P) PLSB_CUDA(cudaMemcpy2DAsync(P, kb, Pd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
     if (R) PLSB_CUDA(cudaMemcpy2DAsync(R, kb, Rd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
     if (Q) PLSB_CUDA(cudaMemcpyAsync(Q, Qd.p, (size_t)A * M * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    if (wantT) PLSB_CUDA(cudaMemcpyAsync(T, Td.p, (size_t)A * N * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (wantT && !streamT) PLSB_CUDA(cudaMemcpyAsync(T, Td.p, (size_t)A * N * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (streamT) PLSB_CUDA(cudaStreamSynchronize(c->copy_stream));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
     if (ds->sharded) PLSB_TRY(xchg_check(c));
     return PLSB_OK;

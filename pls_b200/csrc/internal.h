@@ -12,6 +12,9 @@ struct plsb_ctx {
     int sm_count = 148;
     size_t smem_optin = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // H2D / D2H transfers that overlap kernels on `stream`
+    cudaEvent_t xfer_ev[4] = {nullptr, nullptr, nullptr, nullptr};   // upload: copied[2], transposed[2]
+    cudaEvent_t col_ev = nullptr;         // fit: "column a of T is complete"
     // scratch for cross-CTA partial sums (grown on demand)
     double *part = nullptr;
     size_t part_bytes = 0;
