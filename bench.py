@@ -105,6 +105,34 @@ def cpu_reference_cv(n_sample):
     return nthr / (sec * C5["N"] / n_sample), nthr, sec
 
 
+def small_cv_legs(ctx):
+    """C2 (nir/octane 60 x 401, A = 10, LOO: 60 folds) and C3 (PLS2 60 x 399, Y x3, A = 10, LSO: 1000 folds of 18 held-out
+    rows) from the committed fixtures (tests/golden/, generated from the reference's own CSV files): fits/s through
+    plsb_cv_folds with host index lists in and the residual block back on the host, PRESS checked against the fixture."""
+    import numpy as np
+    from pls_b200 import _capi
+    out = {}
+    gdir = os.path.join(ROOT, "tests", "golden")
+    for name, key in (("c2_nir_octane", "loo"), ("c3_nir_pls2", "lso")):
+        g = np.load(os.path.join(gdir, name + ".npz"))
+        X, Y = np.asfortranarray(g["X"]), np.asfortranarray(g["Y"])
+        te = np.arange(X.shape[0], dtype=np.int64).reshape(-1, 1) if key == "loo" else np.ascontiguousarray(g["lso_test"], dtype=np.int64)
+        ds = _capi.Dataset(ctx, X, Y)
+        E = ds.cv_folds(10, 0, te)
+        reps = 20
+        ctx.sync(); t0 = time.perf_counter()
+        for _ in range(reps):
+            E = ds.cv_folds(10, 0, te)
+        ctx.sync(); sec = (time.perf_counter() - t0) / reps
+        press = (E.reshape(Y.shape[1], -1, 10) ** 2).sum(axis=1)
+        want = g[key + "_ress"] if (key + "_ress") in g.files else None
+        err = float(np.abs(press - want).max() / np.abs(want).max()) if want is not None else None
+        out[name] = {"folds": int(te.shape[0]), "held_out_rows": int(te.shape[1]), "fits_per_s": te.shape[0] / sec,
+                     "ms_per_call": sec * 1e3, "press_rel_err_vs_reference": err}
+        ds.close()
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -205,6 +233,23 @@ def run_ours(args):
                 "other_kernels_ms_per_fit": {"xty_pass": xty_ms / max(nfit, 1), "steps": step_ms / max(nfit, 1),
                                              "partial_reductions": red_ms / max(nfit, 1)}}
 
+    # ---- the one dense contraction of a KERNEL_TYPE2 fit at C4: XX = X'X (pls.cpp:398) on the FP64 tensor cores -----
+    xtx = None
+    if not args.no_xtx:
+        ds.xtx(download=False)                                   # warm-up
+        ctx.profile(True); ctx.profile_reset()
+        ds.xtx(download=False)
+        xtx_ms, _ = ctx.profile_get("xtx")
+        ctx.profile(False)
+        if dist is not None:
+            t = torch.tensor([xtx_ms], device="cuda", dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            xtx_ms = t.item()
+        issued = float(N) * K * (K + 128)                        # SYRK: upper-triangular 128-wide tiles only
+        xtx = {"workload": "XX = X'X of the C4 matrix (rows sharded), incl. the cross-rank sum", "ms": xtx_ms,
+               "tflops_as_reference_counts_2NK2": 2.0 * N * K * K / (xtx_ms * 1e-3) / 1e12,
+               "tflops_issued_syrk": issued / (xtx_ms * 1e-3) / 1e12}
+
     # ---- end to end through the public API with HOST buffers (upload + fit + results back) --------------
     e2e = None
     if not args.no_e2e:
@@ -246,7 +291,7 @@ def run_ours(args):
         te = np.arange(n5, dtype=np.int64).reshape(-1, 1)
         f0, f1 = sharding.fold_shard(n5, rank, world)
         E = np.zeros((m5, a5, n5))
-        ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=min(256, f1 - f0), out=E)    # warm-up wave
+        ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=min(4096, f1 - f0), out=E)   # warm-up: one full wave (same buffers as the timed call)
         ctx.profile(True); ctx.profile_reset()
         barrier()
         t0 = time.perf_counter()
@@ -288,6 +333,14 @@ def run_ours(args):
             except Exception as e:
                 cv["cpu_baseline"] = {"error": repr(e)}
 
+    # ---- configs 2 and 3: small-data CV (60 x ~400 spectra), one CTA per fold, all folds of a call in one wave -----
+    cv_small = None
+    if rank == 0 and not args.no_cv:
+        try:
+            cv_small = small_cv_legs(ctx)
+        except Exception as e:
+            cv_small = {"error": repr(e)}
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         try:
@@ -304,7 +357,7 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "parallelism": f"rows sharded over {world} rank(s)",
                            "l2": "inputs (16.4 GB of X per fit pass) are larger than L2; no flush needed"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cv": cv, "gpu_launches": int(launches), "clocks": clocks,
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cv": cv, "cv_small": cv_small, "xtx_c4": xtx, "gpu_launches": int(launches), "clocks": clocks,
                 "device_ms_per_step": dev_ms / max(nfit, 1)}
         print(json.dumps(line), flush=True)
     if dist is not None:
@@ -323,6 +376,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-cv", action="store_true")
+    ap.add_argument("--no-xtx", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -155,7 +155,8 @@ int plsb_lso_folds(int64_t N, double test_fraction, int64_t num_trials, uint32_t
 #define PLSB_PROF_FIT_TOTAL 6    /* whole fit, device side */
 #define PLSB_PROF_UPLOAD 7       /* H2D + layout transform */
 #define PLSB_PROF_REDUCE 8      /* cross-CTA partial-row sums after a pass */
-#define PLSB_PROF_NSLOTS 9
+#define PLSB_PROF_SCORES 9      /* DMMA scores S = X R */
+#define PLSB_PROF_NSLOTS 10
 int plsb_profile_enable(plsb_ctx_t ctx, int on);
 int plsb_profile_reset(plsb_ctx_t ctx);
 /* total milliseconds and launch count accumulated in a slot since the last reset */

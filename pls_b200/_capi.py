@@ -29,7 +29,7 @@ SYMBOLS = [
     "plsb_profile_enable", "plsb_profile_reset", "plsb_profile_get", "plsb_launch_count",
 ]
 
-PROF = dict(pass_fused=0, pass_xty=1, step=2, xtx=3, cv_gemm=4, cv_fold=5, fit_total=6, upload=7, reduce=8)
+PROF = dict(pass_fused=0, pass_xty=1, step=2, xtx=3, cv_gemm=4, cv_fold=5, fit_total=6, upload=7, reduce=8, scores=9)
 
 
 class PlsbError(RuntimeError):

@@ -26,6 +26,7 @@ struct GemmArgs {
     double *part;                   // [splitk][ntiles][BM*BN]
     int syrk;
     int transC;                     // write C[n*ldc + m] instead of C[m*ldc + n]
+    int accum;                      // C += product (through the partial-tile reduction) instead of C = product
     double *C; int64_t ldc;         // direct output when splitk == 1
 };
 
@@ -128,7 +129,7 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
         }
     }
     cp_async_wait<0>();
-    if (g.splitk == 1 && !g.syrk) {  // no partials needed: write the product directly
+    if (g.splitk == 1 && !g.syrk && !g.accum) {  // no partials needed: write the product directly
 #pragma unroll
         for (int i = 0; i < 8; ++i)
 #pragma unroll
@@ -166,6 +167,7 @@ __global__ void __launch_bounds__(256) gemm_reduce_kernel(const GemmArgs g, doub
         const int m = tm * GM_BM + row, n = tn * GM_BN + col;
         if (m >= g.M || n >= g.N) continue;
         double s = 0.0;
+        if (g.accum) s = g.transC ? C[(int64_t)n * ldc + m] : C[(int64_t)m * ldc + n];
         for (int sp = 0; sp < g.splitk; ++sp) s += g.part[((size_t)sp * g.ntiles + tile) * (GM_BM * GM_BN) + e];
         if (g.transC) C[(int64_t)n * ldc + m] = s;
         else C[(int64_t)m * ldc + n] = s;
@@ -176,12 +178,12 @@ __global__ void __launch_bounds__(256) gemm_reduce_kernel(const GemmArgs g, doub
 // C (M x N, row-major, ldc) = A' B.  syrk: A == B, M == N, C symmetric.  b_nmajor: B given as N x Kd.
 // transC: store C transposed (N x M, row-major).
 int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
-                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot) {
+                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate) {
     if (M == 0 || N == 0) return PLSB_OK;
     PLSB_ARG((lda % 2) == 0 && (ldb % 2) == 0, "gemm: leading dimensions must be even");
     GemmArgs g{};
     g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.Kd = Kd; g.M = M; g.N = N; g.syrk = syrk ? 1 : 0;
-    g.transC = transC ? 1 : 0; g.C = C; g.ldc = ldc;
+    g.transC = transC ? 1 : 0; g.C = C; g.ldc = ldc; g.accum = accumulate ? 1 : 0;
     g.tiles_m = (int)ceil_div(M, GM_BM);
     g.tiles_n = (int)ceil_div(N, GM_BN);
     g.ntiles = syrk ? g.tiles_m * (g.tiles_m + 1) / 2 : g.tiles_m * g.tiles_n;
@@ -192,7 +194,7 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
     if (want < 1) want = 1;
     g.k_per_split = round_up(ceil_div(Kd > 0 ? Kd : 1, want), GM_BK);
     g.splitk = (int)ceil_div(Kd > 0 ? Kd : 1, g.k_per_split);
-    const bool direct = g.splitk == 1 && !syrk;
+    const bool direct = g.splitk == 1 && !syrk && !accumulate;
     if (!direct) {
         const size_t pbytes = (size_t)g.splitk * g.ntiles * GM_BM * GM_BN * sizeof(double);
         PLSB_TRY(ensure_part(c, pbytes));

@@ -116,7 +116,9 @@ int launch_symv(plsb_ctx *c, const double *G, int64_t ldg, int K, const double *
 
 // ---- FP64 DMMA contraction (gemm.cu) --------------------------------------------------------------
 int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
-                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot);
+                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate = false);
+// S (component-major A x lds) = X R for row-major X (N x ldk) and component-major R (A x ldk): DMMA (scores.cu)
+int launch_scores(plsb_ctx *c, const double *X, int64_t N, int ldk, const double *R, int A, double *S, int64_t lds);
 int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg);
 
 // ---- synthetic data (synth.cu) ----------------------------------------------------------------

@@ -125,7 +125,11 @@ static int scores_device(plsb_ctx *c, const double *R, int64_t K, int64_t comp, 
     PLSB_TRY(upload_cm_to_rm(c, Xn, ldx, Nn, K, Xd.p, ldk, false));
     PLSB_CUDA(cudaMemcpy2DAsync(Rd.p, (size_t)ldk * 8, R, (size_t)K * 8, (size_t)K * 8, (size_t)comp,
                                 cudaMemcpyHostToDevice, c->stream));
-    if (Nn > 0) {
+    // DMMA path (scores.cu); PLSB_SCORES_FMA=1 keeps the FMA kernel for A/B runs
+    const char *fma = getenv("PLSB_SCORES_FMA");
+    if (Nn > 0 && !(fma && *fma == '1')) {
+        PLSB_TRY(launch_scores(c, Xd.p, Nn, (int)ldk, Rd.p, (int)comp, Sd.p, Nn));
+    } else if (Nn > 0) {
         scores_kernel<<<(unsigned)ceil_div(Nn, 8 * PR_RW), 256, 0, c->stream>>>(Xd.p, Nn, (int)ldk, (int)K, Rd.p,
                                                                                (int)comp, Sd.p);
         c->launches++;
