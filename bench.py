@@ -266,19 +266,27 @@ def run_ours(args):
                                              _capi.P(Tt)))
             dsh.close()
         one()
+        ctx.profile(True); ctx.profile_reset()
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.e2e_steps):
             one()
         barrier()
         e2e_s = (time.perf_counter() - t0) / args.e2e_steps
+        up_ms, nup = ctx.profile_get("upload"); fit_ms, nf = ctx.profile_get("fit_total")
+        sc_ms, _ = ctx.profile_get("scores"); pf_ms, npf = ctx.profile_get("pass_fused")
+        ctx.profile(False)
         if dist is not None:
             t = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e2e_s = t.item()
         e2e = {"value": 1.0 / e2e_s, "unit": "fits/s", "h2d_bytes_per_step": int(8 * rows * (K + M)),
                "d2h_bytes_per_step": int(8 * (3 * K * A + M * A + rows * A)), "ms_per_step": e2e_s * 1e3,
-               "steps": args.e2e_steps, "what": "plsb_dataset_create(pinned host X,Y) + plsb_fit + W,P,R,Q,T to host"}
+               "steps": args.e2e_steps, "what": "plsb_dataset_create(pinned host X,Y) + plsb_fit + W,P,R,Q,T to host",
+               "device_ms_rank0": {"upload_incl_xtx_xty_under_the_transfer": up_ms / max(args.e2e_steps, 1),
+                                   "fit_after_upload": fit_ms / max(nf, 1), "of_which_scores_T": sc_ms / max(nf, 1)},
+               "path": ("X'X and X'Y accumulated on the tensor cores while the rows cross PCIe; components from the "
+                        "L2-resident X'X; one DMMA pass T = X R") if npf == 0 else "streaming passes (one read of X per component)"}
 
     # ---- config 5: full leave-one-out CV, 20 000 fits of 20000 x 4096 (A = 64), folds sharded over the ranks -----
     cv = None

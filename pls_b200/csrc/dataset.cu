@@ -45,6 +45,68 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
     return rc;
 }
 
+// Host column-major X -> device row-major X in ROW blocks (strided 2-D H2D copies on the copy stream, two staging
+// buffers), and while block i+1 crosses PCIe the tensor cores add block i's contribution to XX = X'X (SYRK, DMMA).
+// The upload is PCIe-bound (~55 GB/s) and X'X needs N*K*(K+128) flops at ~28 TFLOP/s: for K <= ~3000 the whole
+// cross-product build hides under the transfer, and a fit that follows needs no further pass over X except the
+// one that forms the scores (fit.cu).  SURVEY 8(f)-3: chunked H2D overlapped with the cross-product pass.
+static bool gram_on_upload(int64_t N, int64_t K) {
+    const char *e = getenv("PLSB_UPLOAD_GRAM");
+    if (e && *e == '0') return false;
+    if (e && *e == '1') return N > 0;
+    return K >= 256 && K <= 3072 && N >= 16 * K && N >= 65536;
+}
+
+static int upload_rows_with_gram(plsb_ctx *c, const double *src, int64_t lds, plsb_dataset *ds) {
+    const int64_t N = ds->N, K = ds->K, ldk = ds->ldk;
+    ds->ldg = round_up(K, 2);
+    PLSB_TRY(dev_alloc(c, (void **)&ds->G, (size_t)K * ds->ldg * sizeof(double)));
+    PLSB_CUDA(cudaMemsetAsync(ds->G, 0, (size_t)K * ds->ldg * sizeof(double), c->stream));
+    PLSB_TRY(dev_alloc(c, (void **)&ds->S0, (size_t)ds->M * ldk * sizeof(double)));
+    PLSB_CUDA(cudaMemsetAsync(ds->S0, 0, (size_t)ds->M * ldk * sizeof(double), c->stream));
+    int64_t nb = (int64_t)(128u << 20) / (K * 8) / 1024 * 1024;
+    if (nb < 1024) nb = 1024;
+    if (nb > N) nb = N;
+    double *stage = nullptr;
+    PLSB_TRY(dev_alloc(c, (void **)&stage, (size_t)2 * nb * K * sizeof(double)));
+    cudaEvent_t *copied = c->xfer_ev, *moved = c->xfer_ev + 2;
+    int rc = PLSB_OK;
+    cudaError_t e = cudaEventRecord(moved[0], c->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(moved[1], c->stream);
+    int64_t i = 0;
+    for (int64_t r0 = 0; r0 < N && rc == PLSB_OK && e == cudaSuccess; r0 += nb, ++i) {
+        const int64_t nr = N - r0 < nb ? N - r0 : nb;
+        const int b = (int)(i & 1);
+        double *buf = stage + (size_t)b * nb * K;
+        e = cudaStreamWaitEvent(c->copy_stream, moved[b], 0);
+        if (e == cudaSuccess)   // K column segments of nr rows each, packed column-major (ld = nr)
+            e = cudaMemcpy2DAsync(buf, (size_t)nr * 8, src + r0, (size_t)lds * 8, (size_t)nr * 8, (size_t)K,
+                                  cudaMemcpyHostToDevice, c->copy_stream);
+        if (e == cudaSuccess) e = cudaEventRecord(copied[b], c->copy_stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, copied[b], 0);
+        if (e != cudaSuccess) break;
+        rc = launch_cm_to_rm(c, buf, nr, nr, K, ds->X + r0 * ldk, ldk, 0);
+        if (rc == PLSB_OK) e = cudaEventRecord(moved[b], c->stream);
+        if (rc == PLSB_OK && e == cudaSuccess)
+            rc = launch_gemm_atb(c, ds->X + r0 * ldk, ldk, ds->X + r0 * ldk, ldk, nr, (int)K, (int)K, ds->G, ds->ldg, true,
+                                 false, false, PLSB_PROF_XTX, true);
+        for (int64_t m0 = 0; m0 < ds->M && rc == PLSB_OK; m0 += 128) {   // S0 += X_b' Y_b (Y is already on the device)
+            const int mc = (int)(ds->M - m0 < 128 ? ds->M - m0 : 128);
+            rc = launch_gemm_atb(c, ds->X + r0 * ldk, ldk, ds->Y + r0 * ds->ldm + m0, ds->ldm, nr, (int)K, mc,
+                                 ds->S0 + m0 * ldk, ldk, false, false, true, PLSB_PROF_PASS_XTY, true);
+        }
+    }
+    if (e != cudaSuccess && rc == PLSB_OK) rc = cuda_fail(e, "upload (H2D, row blocks)", __FILE__, __LINE__);
+    e = cudaStreamSynchronize(c->copy_stream);
+    if (rc == PLSB_OK && e != cudaSuccess) rc = cuda_fail(e, "upload sync", __FILE__, __LINE__);
+    e = cudaStreamSynchronize(c->stream);
+    if (rc == PLSB_OK && e != cudaSuccess) rc = cuda_fail(e, "upload sync", __FILE__, __LINE__);
+    dev_free(c, stage);
+    ds->gram_valid = rc == PLSB_OK;
+    ds->gram_reduced = false;
+    return rc;
+}
+
 static int dataset_alloc(plsb_ctx *c, int64_t N, int64_t K, int64_t M, plsb_dataset **out) {
     PLSB_ARG(c && out, "null argument");
     PLSB_ARG(N >= 0 && K >= 1 && M >= 1, "bad shape N=%lld K=%lld M=%lld", (long long)N, (long long)K, (long long)M);
@@ -77,8 +139,11 @@ static int dataset_fill(plsb_ctx *c, const double *X, int64_t ldx, int64_t N, in
     int rc;
     {
         ProfScope ps(c, PLSB_PROF_UPLOAD);
-        rc = upload_cm_to_rm(c, X, ldx, N, K, ds->X, ds->ldk, on_device);
-        if (rc == PLSB_OK) rc = upload_cm_to_rm(c, Y, ldy, N, M, ds->Y, ds->ldm, on_device);
+        rc = upload_cm_to_rm(c, Y, ldy, N, M, ds->Y, ds->ldm, on_device);
+        if (rc == PLSB_OK) {
+            if (!on_device && gram_on_upload(N, K)) rc = upload_rows_with_gram(c, X, ldx, ds);
+            else rc = upload_cm_to_rm(c, X, ldx, N, K, ds->X, ds->ldk, on_device);
+        }
     }
     if (rc != PLSB_OK) { plsb_dataset_destroy(ds); return rc; }
     *out = ds;
@@ -118,6 +183,8 @@ int plsb_dataset_destroy(plsb_dataset_t ds) {
     cudaStreamSynchronize(ds->ctx->stream);
     dev_free(ds->ctx, ds->X);
     dev_free(ds->ctx, ds->Y);
+    dev_free(ds->ctx, ds->G);
+    dev_free(ds->ctx, ds->S0);
     delete ds;
     return PLSB_OK;
 }
@@ -131,6 +198,7 @@ int plsb_dataset_shape(plsb_dataset_t ds, int64_t *N, int64_t *K, int64_t *M) {
 int plsb_dataset_set_sharded(plsb_dataset_t ds, int sharded) {
     PLSB_ARG(ds, "dataset is null");
     ds->sharded = sharded != 0;
+    ds->gram_agreed = -1;
     return PLSB_OK;
 }
 

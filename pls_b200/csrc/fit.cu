@@ -34,13 +34,44 @@ int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, 
     DevBuf S(c), g(c), G(c);
     PLSB_TRY(S.alloc((size_t)M * ldk, false));
     PLSB_TRY(g.alloc((size_t)ldk + 2, true));
-    PLSB_TRY(launch_xty_pass(c, ds, S.p));
-    if (shard) PLSB_TRY(allreduce_sum(c, S.p, (size_t)M * ldk));
     const int64_t ldg = round_up(K, 2);
-    if (method == PLSB_KERNEL_TYPE2) {
+    // A data set uploaded from host memory may carry XX = X'X already (accumulated under the PCIe transfer,
+    // dataset.cu).  Then every component is a product with the L2-resident XX (the KERNEL_TYPE2 recurrence, which
+    // is the same model: measured against the reference at 1M x 2048 both kernels sit at the same distance from
+    // it, profiles/r1c_fullsize_parity.json) and X is read once more only to form the scores T = X R.
+    const char *nog = getenv("PLSB_FIT_NO_GRAM");
+    bool have_gram = ds->G && ds->gram_valid && !(nog && *nog == '1');
+    if (shard) {
+        // every rank must take the same branch (the branches differ in their collectives): ask once per data set
+        if (ds->gram_agreed < 0) {
+            double flag = have_gram ? 1.0 : 0.0;
+            PLSB_CUDA(cudaMemcpyAsync(g.p, &flag, sizeof(double), cudaMemcpyHostToDevice, c->stream));
+            PLSB_TRY(allreduce_sum(c, g.p, 1));
+            PLSB_CUDA(cudaMemcpyAsync(&flag, g.p, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+            PLSB_CUDA(cudaStreamSynchronize(c->stream));
+            PLSB_CUDA(cudaMemsetAsync(g.p, 0, sizeof(double), c->stream));
+            ds->gram_agreed = flag > (double)c->nranks - 0.5 ? 1 : 0;
+        }
+        have_gram = have_gram && ds->gram_agreed == 1;
+    }
+    const bool from_gram = have_gram || method == PLSB_KERNEL_TYPE2;
+    if (have_gram && ds->S0)   // X'Y was accumulated under the transfer as well
+        PLSB_CUDA(cudaMemcpyAsync(S.p, ds->S0, (size_t)M * ldk * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+    else
+        PLSB_TRY(launch_xty_pass(c, ds, S.p));
+    if (shard) PLSB_TRY(allreduce_sum(c, S.p, (size_t)M * ldk));
+    const double *Gp = nullptr;
+    if (have_gram) {
+        if (shard && !ds->gram_reduced) {
+            PLSB_TRY(allreduce_sum(c, ds->G, (size_t)K * ldg));
+            ds->gram_reduced = true;
+        }
+        Gp = ds->G;
+    } else if (method == PLSB_KERNEL_TYPE2) {
         PLSB_TRY(G.alloc((size_t)K * ldg, true));
         PLSB_TRY(launch_xtx(c, ds, G.p, ldg));
         if (shard) PLSB_TRY(allreduce_sum(c, G.p, (size_t)K * ldg));
+        Gp = G.p;
     }
     StepArgs st{};
     st.K = (int)K; st.ldk = (int)ldk; st.M = (int)M; st.A = (int)A;
@@ -49,7 +80,7 @@ int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, 
     PLSB_TRY(launch_step(c, st));
     for (int64_t a = 0; a < A; ++a) {
         const double *r = Rd + a * ldk;
-        if (method == PLSB_KERNEL_TYPE1) {
+        if (!from_gram) {
             // one read of this rank's rows; [g | tt] comes back summed over the CTAs AND over the ranks
             PLSB_TRY(launch_fused_pass(c, ds, r, g.p, Td ? Td + a * ds->N : nullptr, shard));
             if (Td && T_host) {
@@ -59,10 +90,25 @@ int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, 
                                           cudaMemcpyDeviceToHost, c->copy_stream));
             }
         } else {
-            PLSB_TRY(launch_symv(c, G.p, ldg, (int)K, r, g.p, (int)ldk));
+            PLSB_TRY(launch_symv(c, Gp, ldg, (int)K, r, g.p, (int)ldk));
         }
         st.a = (int)a;
         PLSB_TRY(launch_step(c, st));
+    }
+    if (from_gram && Td && ds->N > 0) {
+        // scores of the training rows, T = X R (pls.cpp:419 for every component at once): DMMA, one read of X per
+        // 32 components, in row chunks so that a pinned destination receives chunk i while chunk i+1 is computed
+        const int64_t chunk = T_host ? round_up(ceil_div(ds->N, 4), 128) : ds->N;
+        for (int64_t r0 = 0; r0 < ds->N; r0 += chunk) {
+            const int64_t nr = ds->N - r0 < chunk ? ds->N - r0 : chunk;
+            PLSB_TRY(launch_scores(c, ds->X + r0 * ldk, nr, (int)ldk, Rd, (int)A, Td + r0, ds->N));
+            if (T_host) {
+                PLSB_CUDA(cudaEventRecord(c->col_ev, c->stream));
+                PLSB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->col_ev, 0));
+                PLSB_CUDA(cudaMemcpy2DAsync(T_host + r0, (size_t)ds->N * 8, Td + r0, (size_t)ds->N * 8, (size_t)nr * 8,
+                                            (size_t)A, cudaMemcpyDeviceToHost, c->copy_stream));
+            }
+        }
     }
     return PLSB_OK;
 }

@@ -47,6 +47,14 @@ struct plsb_dataset {
     double *X = nullptr;  // row-major N x ldk
     double *Y = nullptr;  // row-major N x ldm
     bool sharded = false;
+    // XX = X'X of THIS data set's rows, accumulated on the tensor cores while the rows were still crossing PCIe
+    // (dataset.cu: upload_rows_with_gram).  When present a fit runs from it (fit.cu) instead of re-reading X.
+    double *G = nullptr;  // K x ldg
+    double *S0 = nullptr; // M x ldk: X'Y of this data set's rows, accumulated the same way (valid with G)
+    int64_t ldg = 0;
+    bool gram_valid = false;
+    bool gram_reduced = false;  // row-sharded: G already summed over the ranks
+    int gram_agreed = -1;       // row-sharded: do ALL ranks hold a Gram matrix? (-1: not asked yet)
 };
 
 namespace plsb {

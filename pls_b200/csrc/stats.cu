@@ -202,6 +202,7 @@ int plsb_dataset_zscore(plsb_dataset_t ds, double *x_mean, double *x_stdev, doub
     Buf mx(c), sx(c), my(c), sy(c);
     PLSB_TRY(mx.alloc((size_t)ds->ldk, true)); PLSB_TRY(sx.alloc((size_t)ds->ldk, true));
     PLSB_TRY(my.alloc((size_t)ds->ldm, true)); PLSB_TRY(sy.alloc((size_t)ds->ldm, true));
+    ds->gram_valid = false; ds->gram_agreed = -1;   // X changes in place: a Gram matrix accumulated during the upload no longer applies
     PLSB_TRY(device_zscore(c, ds->X, ds->N, (int)ds->ldk, (int)ds->K, mx.p, sx.p));
     PLSB_TRY(device_zscore(c, ds->Y, ds->N, (int)ds->ldm, (int)ds->M, my.p, sy.p));
     if (x_mean) PLSB_CUDA(cudaMemcpyAsync(x_mean, mx.p, (size_t)ds->K * 8, cudaMemcpyDeviceToHost, c->stream));

@@ -112,6 +112,36 @@ def test_xty_dmma_path(ctx, N, K, M):
     ds.close()
 
 
+@pytest.mark.parametrize("N,K,M,A", [(3000, 300, 3, 8), (1500, 77, 1, 6), (2048, 512, 8, 10), (5000, 1030, 2, 5)])
+def test_fit_from_gram_accumulated_during_upload(ctx, N, K, M, A, monkeypatch):
+    """Host data uploaded in row blocks with X'X accumulated on the tensor cores under the transfer (dataset.cu):
+    the fit that follows runs from X'X and forms T = X R with the DMMA scores kernel.  Same model as plsr
+    (pls.cpp:390-437, KERNEL_TYPE1 request), ragged last block, odd K."""
+    monkeypatch.setenv("PLSB_UPLOAD_GRAM", "1")
+    X, Y = port.synth(7000 + N + K, N, K, M, L=max(A, 4))
+    want = port.fit(X, Y, A, 0)
+    ds = _capi.Dataset(ctx, X, Y)
+    ctx.profile(True); ctx.profile_reset()
+    got = ds.fit(A, 0)
+    assert ctx.profile_get("pass_fused")[1] == 0 and ctx.profile_get("scores")[1] >= 1     # no streaming pass ran
+    ctx.profile(False)
+    assert_state_close(got, want, rtol=1e-8 if K > 1000 else RTOL)
+    assert relerr(port.coefficients(got["R"], got["Q"], A), port.coefficients(want["R"], want["Q"], A)) <= RTOL
+    assert relerr(ds.xtx(), X.T @ X) <= 1e-12
+    Xd, Yd = ds.download()
+    assert np.array_equal(Xd, X) and np.array_equal(Yd, Y)
+    monkeypatch.setenv("PLSB_FIT_NO_GRAM", "1")                     # the streaming-pass path on the same data set
+    again = ds.fit(A, 0)
+    assert_state_close(again, got, rtol=1e-8 if K > 1000 else RTOL)
+    ds.zscore()                                                     # X changes in place: the Gram matrix is dropped
+    monkeypatch.delenv("PLSB_FIT_NO_GRAM")
+    z = ds.fit(A, 0)
+    Xz = (X - X.mean(0)) / X.std(0, ddof=1); Yz = (Y - Y.mean(0)) / Y.std(0, ddof=1)
+    wz = port.fit(np.asfortranarray(Xz), np.asfortranarray(Yz), A, 0)
+    assert relerr(port.coefficients(z["R"], z["Q"], A), port.coefficients(wz["R"], wz["Q"], A)) <= 1e-8
+    ds.close()
+
+
 def test_type1_equals_type2_and_invariants(ctx):
     ds = _capi.Dataset(ctx, synth=(7, 0, 5000, 384, 4, 16))
     a = ds.fit(12, 0); b = ds.fit(12, 1)
