@@ -67,6 +67,46 @@ def test_row_sharded_fit_matches_single_gpu(method):
 
 
 @needs2
+@pytest.mark.parametrize("mixed", [False, True])
+def test_row_sharded_fit_from_gram_accumulated_during_upload(mixed, monkeypatch):
+    """Row shards uploaded with X'X / X'Y accumulated under the transfer (dataset.cu): the partial Gram matrices are
+    all-reduced once and the fit runs from the sum.  mixed: one rank has no Gram matrix (device-generated shard) —
+    the ranks must agree on the streaming-pass path instead of dead-locking in different collectives."""
+    G = 2
+    seed, N, K, M, A = 4242, 6000, 300, 3, 9
+    X, Y = port.synth(seed, N, K, M)
+    monkeypatch.setenv("PLSB_UPLOAD_GRAM", "1")
+    ctxs = [_capi.Context(i) for i in range(G)]
+    uid = _capi.Context.unique_id()
+    b = shard_bounds(N, G)
+    out = [None] * G
+
+    def rank(i):
+        ctxs[i].comm_init(i, G, uid)
+        if mixed and i == 1:
+            ds = _capi.Dataset(ctxs[i], synth=(seed, b[i], b[i + 1] - b[i], K, M, 16), sharded=True)
+        else:
+            ds = _capi.Dataset(ctxs[i], X[b[i]:b[i + 1]], Y[b[i]:b[i + 1]], sharded=True)
+        ctxs[i].profile(True); ctxs[i].profile_reset()
+        out[i] = ds.fit(A, 0)
+        out[i]["passes"] = ctxs[i].profile_get("pass_fused")[1]
+        out[i] = dict(out[i], again=ds.fit(A, 0))          # second fit: the Gram sum must not be reduced twice
+        ds.close()
+
+    th = [threading.Thread(target=rank, args=(i,)) for i in range(G)]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert all(o is not None for o in out)
+    assert all((o["passes"] > 0) == mixed for o in out)
+    want = port.fit(X, Y, A, 0)
+    for key in ("first", "again"):
+        got = {k: (out[0] if key == "first" else out[0]["again"])[k] for k in "WPRQ"}
+        got["T"] = np.vstack([(o if key == "first" else o["again"])["T"] for o in out])
+        assert_state_close(got, want)
+        assert relerr(port.coefficients(got["R"], got["Q"], A), port.coefficients(want["R"], want["Q"], A)) <= RTOL
+    [c.close() for c in ctxs]
+
+
+@needs2
 def test_fold_sharded_cv_matches_single_gpu():
     G = min(ngpu(), 4)
     g = load_golden("c3_nir_pls2")
