@@ -105,7 +105,7 @@ def cpu_reference_cv(n_sample):
     return nthr / (sec * C5["N"] / n_sample), nthr, sec
 
 
-def small_cv_legs(ctx):
+def small_cv_legs(ctx, with_cpu=True):
     """C2 (nir/octane 60 x 401, A = 10, LOO: 60 folds) and C3 (PLS2 60 x 399, Y x3, A = 10, LSO: 1000 folds of 18 held-out
     rows) from the committed fixtures (tests/golden/, generated from the reference's own CSV files): fits/s through
     plsb_cv_folds with host index lists in and the residual block back on the host, PRESS checked against the fixture."""
@@ -130,6 +130,27 @@ def small_cv_legs(ctx):
         out[name] = {"folds": int(te.shape[0]), "held_out_rows": int(te.shape[1]), "fits_per_s": te.shape[0] / sec,
                      "ms_per_call": sec * 1e3, "press_rel_err_vs_reference": err}
         ds.close()
+        if with_cpu:
+            # the reference's plsr per fold (inner A = 10; its own cv_LOO/cv_LSO extract K components per fold and
+            # are ~40x slower for the same first 10), folds split over all host threads
+            try:
+                from concurrent.futures import ThreadPoolExecutor
+                from oracle import ref
+                if ref.available():
+                    nthr = os.cpu_count() or 1
+                    nf = te.shape[0]
+                    tr = np.ascontiguousarray(g["lso_train"], dtype=np.int64) if key == "lso" else None
+                    cuts = [nf * i // nthr for i in range(nthr + 1)]
+                    jobs = [(cuts[i], cuts[i + 1]) for i in range(nthr) if cuts[i + 1] > cuts[i]]
+                    t0 = time.perf_counter()
+                    with ThreadPoolExecutor(len(jobs)) as ex:
+                        list(ex.map(lambda ab: ref.cv_folds(X, Y, 10, 0, te[ab[0]:ab[1]],
+                                                            None if tr is None else tr[ab[0]:ab[1]]), jobs))
+                    csec = time.perf_counter() - t0
+                    out[name]["cpu_baseline"] = {"value": nf / csec, "unit": "fits/s", "cores": len(jobs), "kind": "reference",
+                                                 "sample": f"all {nf} folds, reference plsr per fold (inner A = 10), {csec:.2f} s"}
+            except Exception as e:
+                out[name]["cpu_baseline"] = {"error": repr(e)}
     return out
 
 
@@ -345,7 +366,7 @@ def run_ours(args):
     cv_small = None
     if rank == 0 and not args.no_cv:
         try:
-            cv_small = small_cv_legs(ctx)
+            cv_small = small_cv_legs(ctx, with_cpu=(world == 1 and not args.no_cpu))
         except Exception as e:
             cv_small = {"error": repr(e)}
 
