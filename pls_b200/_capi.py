@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libplsb.so")
+LIB_PATH = os.environ.get("PLSB_LIB") or os.path.join(_HERE, "libplsb.so")   # PLSB_LIB: dev A/B builds of the same library
 _lib = None
 
 _dp = C.POINTER(C.c_double)

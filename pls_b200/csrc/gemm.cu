@@ -13,7 +13,18 @@
 
 namespace plsb {
 
-constexpr int GM_BM = 128, GM_BN = 128, GM_BK = 16, GM_LD = 132, GM_NT = 256, GM_STAGES = 3;
+#ifndef PLSB_GM_BK       // tuning knobs (tools/gemm_variants.sh builds A/B libraries with other values)
+#define PLSB_GM_BK 32
+#endif
+#ifndef PLSB_GM_STAGES
+#define PLSB_GM_STAGES 3
+#endif
+#ifndef PLSB_GM_NT
+#define PLSB_GM_NT 256
+#endif
+constexpr int GM_BM = 128, GM_BN = 128, GM_BK = PLSB_GM_BK, GM_LD = 132, GM_NT = PLSB_GM_NT, GM_STAGES = PLSB_GM_STAGES;
+constexpr int GM_WM = GM_BM / (GM_NT / 32 / 4);   // rows per warp tile: 4 warps across the 128 columns, the rest down
+constexpr int GM_MI = GM_WM / 8;                  // 8-row fragments per warp tile
 constexpr int GM_LDBN = GM_BK + 4;                       // n-major B tile: [BN][BK + 4]
 constexpr int GM_BS_KMAJOR = GM_BK * GM_LD, GM_BS_NMAJOR = GM_BN * GM_LDBN;
 
@@ -92,9 +103,9 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
         }
     };
 
-    double acc[8][4][2];
+    double acc[GM_MI][4][2];
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < GM_MI; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
 
@@ -102,7 +113,7 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
         if (s < nk) load_stage(s, s);
         cp_async_commit();
     }
-    const int wm = (warp >> 2) * 64, wn = (warp & 3) * 32;
+    const int wm = (warp >> 2) * GM_WM, wn = (warp & 3) * 32;
     const int fk = lane & 3, fr = lane >> 2;
     for (int kt = 0; kt < nk; ++kt) {
         cp_async_wait<GM_STAGES - 2>();
@@ -116,14 +127,14 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
         const double *bs = Bs + (size_t)(kt % GM_STAGES) * BS_STAGE;
 #pragma unroll
         for (int kk = 0; kk < GM_BK / 4; ++kk) {
-            double a[8], b[4];
+            double a[GM_MI], b[4];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] = as[(kk * 4 + fk) * GM_LD + wm + i * 8 + fr];
+            for (int i = 0; i < GM_MI; ++i) a[i] = as[(kk * 4 + fk) * GM_LD + wm + i * 8 + fr];
 #pragma unroll
             for (int j = 0; j < 4; ++j)
                 b[j] = B_NMAJOR ? bs[(wn + j * 8 + fr) * GM_LDBN + kk * 4 + fk] : bs[(kk * 4 + fk) * GM_LD + wn + j * 8 + fr];
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
+            for (int i = 0; i < GM_MI; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
@@ -131,7 +142,7 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
     cp_async_wait<0>();
     if (g.splitk == 1 && !g.syrk && !g.accum) {  // no partials needed: write the product directly
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+        for (int i = 0; i < GM_MI; ++i)
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 const int m = m_base + wm + i * 8 + fr, n = n_base + wn + j * 8 + fk * 2;
@@ -148,7 +159,7 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
     }
     double *out = g.part + ((size_t)split * g.ntiles + tile) * (GM_BM * GM_BN);
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < GM_MI; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int row = wm + i * 8 + fr, col = wn + j * 8 + fk * 2;
