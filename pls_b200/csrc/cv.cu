@@ -90,6 +90,222 @@ __global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
     next_weights<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, sh);
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Fused per-component fold kernel (1024 <= K <= 4096, M <= 8, test_size <= 256): the same algebra as above with every
+// thread OWNING its columns {tid, tid + NT, ...} across the phases, so that vectors stay in registers between them
+// and the small matrix S_f is swept three times per component instead of ~nine (q = S'r; deflation fused with the
+// Gram matrix S'S of the deflated S — its entries are accumulated from the values just computed; w = S q):
+// 24 instead of 38 K-vectors of per-fold traffic besides the P/R stream of the orthogonalisation.
+// ------------------------------------------------------------------------------------------------------------------
+#ifndef PLSB_CV_FNT
+#define PLSB_CV_FNT 256
+#endif
+constexpr int CV_FNT = PLSB_CV_FNT;          // threads of the fused kernel
+constexpr int CV_KPT = 4096 / CV_FNT;        // columns per thread: K <= 4096
+
+// sums NV per-thread values over the CTA; every thread receives all NV totals (fixed order: deterministic)
+template <int NV>
+__device__ __forceinline__ void block_sum_vec(double (&v)[NV], double *red /* [CV_FNT/32 + 1][NV] */) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int NW = CV_FNT / 32;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = warp_sum(v[i]);
+    __syncthreads();   // protect red[] from its previous use
+    if (lane == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) red[warp * NV + i] = v[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < NV) {   // one thread per value adds the warps' sums in warp order
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) t += red[w * NV + threadIdx.x];
+        red[NW * NV + threadIdx.x] = t;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < NV; ++i) v[i] = red[NW * NV + i];
+}
+
+#ifndef PLSB_CV_MINB
+#define PLSB_CV_MINB 4
+#endif
+template <int MM>
+__global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT : 1) cv_fold_fused_kernel(const CvArgs v) {
+    constexpr int NP = MM * (MM + 1) / 2;
+    __shared__ StepSmem<CV_FNT> sh;
+    __shared__ double red[(CV_FNT / 32 + 1) * (NP > MM ? NP : MM)];
+    __shared__ double qe[MM];
+    const int tid = threadIdx.x;
+    const int f = blockIdx.x;
+    const int64_t gf = (int64_t)v.f0 + f;
+    const int64_t *h = v.test_idx + gf * v.ts;
+    const int K = v.K, ldk = v.ldk, M = v.M, a = v.a, ts = v.ts;
+    double *Sf = v.S + (size_t)f * M * ldk;
+    double *Pf = v.P + (size_t)f * v.A * ldk;
+    double *Rf = v.R + (size_t)f * v.A * ldk;
+    const double *r = Rf + (size_t)a * ldk;
+    const double *g = v.Gr + (size_t)f * ldk;
+    double *pa = Pf + (size_t)a * ldk;
+    double *U = v.U + (size_t)f * ts;
+
+    // ---- u = X_H r (held-out scores), then the downdate g = (X'X) r - X_H' u in registers; tt = r'g ----------------
+    warp_dots<CV_FNT>(ts, K, [&](int i) { return v.X + h[i] * (int64_t)ldk; }, [&](int) { return r; }, sh.c);
+    __syncthreads();
+    double gv[CV_KPT];
+    double tt1[1] = {0.0};
+#pragma unroll
+    for (int j = 0; j < CV_KPT; ++j) {
+        const int k = tid + CV_FNT * j;
+        gv[j] = k < K ? g[k] : 0.0;
+    }
+    for (int i = 0; i < ts; ++i) {          // all of a thread's columns of one held-out row in flight at once
+        const double ci = sh.c[i];
+        const double *xr = v.X + h[i] * (int64_t)ldk;
+#pragma unroll
+        for (int j = 0; j < CV_KPT; ++j) {
+            const int k = tid + CV_FNT * j;
+            if (k < K) gv[j] -= ci * xr[k];
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < CV_KPT; ++j) {
+        const int k = tid + CV_FNT * j;
+        if (k < K) tt1[0] = fma(r[k], gv[j], tt1[0]);
+    }
+    for (int i = tid; i < ts; i += CV_FNT) U[i] = sh.c[i];
+    block_sum_vec<1>(tt1, red);
+    const double tt = tt1[0];
+
+    // ---- p = g / tt (stored), q = S'r / tt ---------------------------------------------------------------------------
+    double qm[MM];
+#pragma unroll
+    for (int m = 0; m < MM; ++m) qm[m] = 0.0;
+#pragma unroll
+    for (int j = 0; j < CV_KPT; ++j) {
+        const int k = tid + CV_FNT * j;
+        if (k < K) {
+            pa[k] = gv[j] / tt;
+            const double rk = r[k];
+#pragma unroll
+            for (int m = 0; m < MM; ++m)
+                if (m < M) qm[m] = fma(Sf[(size_t)m * ldk + k], rk, qm[m]);
+        }
+    }
+    for (int k = K + tid; k < ldk; k += CV_FNT) pa[k] = 0.0;
+    block_sum_vec<MM>(qm, red);
+#pragma unroll
+    for (int m = 0; m < MM; ++m) qm[m] = qm[m] / tt;
+    if (tid == 0) {
+#pragma unroll
+        for (int m = 0; m < MM; ++m) sh.q[m] = qm[m];
+    }
+
+    // ---- S -= tt p q' fused with the Gram matrix of the deflated S ---------------------------------------------------
+    double gp[NP];
+#pragma unroll
+    for (int i = 0; i < NP; ++i) gp[i] = 0.0;
+#pragma unroll
+    for (int j = 0; j < CV_KPT; ++j) {
+        const int k = tid + CV_FNT * j;
+        if (k < K) {
+            const double tp = tt * pa[k];
+            double sv[MM];
+#pragma unroll
+            for (int m = 0; m < MM; ++m) {
+                sv[m] = 0.0;
+                if (m < M) {
+                    sv[m] = Sf[(size_t)m * ldk + k] - tp * qm[m];
+                    Sf[(size_t)m * ldk + k] = sv[m];
+                }
+            }
+            int pi = 0;
+#pragma unroll
+            for (int u = 0; u < MM; ++u)
+#pragma unroll
+                for (int w2 = u; w2 < MM; ++w2) { gp[pi] = fma(sv[u], sv[w2], gp[pi]); ++pi; }
+        }
+    }
+    // residuals of the held-out rows with a+1 components: e_a = e_{a-1} - u q_a'
+    __syncthreads();   // sh.q visible
+    for (int e = tid; e < ts * M; e += CV_FNT) {
+        const int i = e / M, m = e % M;
+        const int64_t row = gf * ts + i;
+        const double prev = (a == 0) ? v.Y[h[i] * (int64_t)v.ldm + m] : v.E[((size_t)m * v.A + (a - 1)) * v.rows_local + row];
+        v.E[((size_t)m * v.A + a) * v.rows_local + row] = prev - sh.c[i] * sh.q[m];
+    }
+    const int an = a + 1;
+    if (an >= v.A) return;
+
+    // ---- next weights: dominant eigenvector of S'S, w = S q / |S q| -------------------------------------------------
+    if (MM > 1) {
+        block_sum_vec<NP>(gp, red);
+        if (tid == 0) {
+            int pi = 0;
+#pragma unroll
+            for (int u = 0; u < MM; ++u)
+#pragma unroll
+                for (int w2 = u; w2 < MM; ++w2) {
+                    if (u < M && w2 < M) { sh.gram[u * M + w2] = gp[pi]; sh.gram[w2 * M + u] = gp[pi]; }
+                    ++pi;
+                }
+        }
+        __syncthreads();
+        if (tid < 32) jacobi_dominant_warp(sh.gram, sh.V, M, qe);
+        __syncthreads();
+    }
+    double wv[CV_KPT];
+    double n1[1] = {0.0};
+#pragma unroll
+    for (int j = 0; j < CV_KPT; ++j) {
+        const int k = tid + CV_FNT * j;
+        double acc = 0.0;
+        if (k < K) {
+            if (MM == 1) acc = Sf[k];
+            else {
+#pragma unroll
+                for (int m = 0; m < MM; ++m)
+                    if (m < M) acc = fma(Sf[(size_t)m * ldk + k], qe[m], acc);
+            }
+            n1[0] = fma(acc, acc, n1[0]);
+        }
+        wv[j] = acc;
+    }
+    block_sum_vec<1>(n1, red);
+    const double nrm = sqrt(n1[0]);
+    double *w = v.w + (size_t)f * ldk;
+#pragma unroll
+    for (int j = 0; j < CV_KPT; ++j) {
+        const int k = tid + CV_FNT * j;
+        if (k < K) { wv[j] = wv[j] / nrm; w[k] = wv[j]; }
+    }
+    __syncthreads();
+    // ---- r = w - sum_j (p_j'w) r_j ------------------------------------------------------------------------------------
+    double *rn = Rf + (size_t)an * ldk;
+    for (int j0 = 0; j0 < an; j0 += 256) {
+        const int nj = an - j0 < 256 ? an - j0 : 256;
+        warp_dots<CV_FNT>(nj, K, [&](int j) { return (const double *)(Pf + (size_t)(j0 + j) * ldk); },
+                         [&](int) { return (const double *)w; }, sh.c);
+        __syncthreads();
+        for (int jj = 0; jj < nj; ++jj) {   // one row of R_f: all of a thread's columns in flight at once
+            const double cj = sh.c[jj];
+            const double *rr = Rf + (size_t)(j0 + jj) * ldk;
+#pragma unroll
+            for (int j = 0; j < CV_KPT; ++j) {
+                const int k = tid + CV_FNT * j;
+                if (k < K) wv[j] -= cj * rr[k];
+            }
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < CV_KPT; ++j) {
+        const int k = tid + CV_FNT * j;
+        if (k < K) rn[k] = wv[j];
+    }
+    for (int k = K + tid; k < ldk; k += CV_FNT) rn[k] = 0.0;
+}
+
 struct CvBuf {
     plsb_ctx *c;
     void *p = nullptr;
@@ -153,6 +369,8 @@ extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t n
     v.S = S.d(); v.P = P.d(); v.R = R.d(); v.w = w.d(); v.Gr = Gr.d(); v.U = U.d(); v.E = Ed.d();
     v.rows_local = rows_local; v.K = (int)K; v.ldk = (int)ldk; v.ldm = (int)ds->ldm; v.M = (int)M; v.A = (int)A;
     v.ts = (int)ts;
+    const char *v1 = getenv("PLSB_CV_V1");   // A/B switch: the phase-by-phase kernel for every launch
+    const bool fused = K >= 1024 && K <= (int64_t)CV_KPT * CV_FNT && M <= 8 && ts <= 256 && !(v1 && *v1 == '1');
     for (int64_t f0 = 0; f0 < nfolds_local; f0 += F) {
         const int nf = (int)(nfolds_local - f0 < F ? nfolds_local - f0 : F);
         v.f0 = (int)f0;
@@ -163,7 +381,14 @@ extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t n
                                          false, true, true, PLSB_PROF_CV_GEMM));
             {
                 ProfScope ps(c, PLSB_PROF_CV_FOLD);
-                cv_fold_kernel<<<nf, CV_NT, 0, c->stream>>>(v);
+                if (a >= 0 && fused) {
+                    if (M == 1) cv_fold_fused_kernel<1><<<nf, CV_FNT, 0, c->stream>>>(v);
+                    else if (M == 2) cv_fold_fused_kernel<2><<<nf, CV_FNT, 0, c->stream>>>(v);
+                    else if (M <= 4) cv_fold_fused_kernel<4><<<nf, CV_FNT, 0, c->stream>>>(v);
+                    else cv_fold_fused_kernel<8><<<nf, CV_FNT, 0, c->stream>>>(v);
+                } else {
+                    cv_fold_kernel<<<nf, CV_NT, 0, c->stream>>>(v);
+                }
             }
             c->launches++;
             PLSB_CUDA(cudaGetLastError());
