@@ -58,6 +58,10 @@ class ClockSampler(threading.Thread):
         self.stop_flag = True
         if self.proc:
             self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:      # a sampler that lingers would keep polling the driver during the later legs
+                self.proc.kill()
         sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
         reasons = set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
