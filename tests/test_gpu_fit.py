@@ -159,6 +159,17 @@ def test_type1_equals_type2_and_invariants(ctx):
     ds.close()
 
 
+@pytest.mark.parametrize("Nn,K,A", [(1, 7, 1), (130, 2049, 33), (257, 512, 8), (1000, 33, 17), (129, 4100, 40)])
+def test_scores_dmma_shapes(ctx, Nn, K, A):
+    """S = X_new R (pls.cpp:439-442) through the DMMA kernel (scores.cu): ragged row tiles, odd K (zero-padded
+    leading dimension), component counts that are not multiples of 8 and exceed one 32-component launch."""
+    rng = np.random.default_rng(Nn + K + A)
+    Xn = np.asfortranarray(rng.standard_normal((Nn, K)))
+    R = np.asfortranarray(rng.standard_normal((K, A)))
+    for comp in sorted({1, A // 2 or 1, A}):
+        assert relerr(_capi.scores(ctx, R, comp, Xn), Xn @ R[:, :comp]) <= 1e-13
+
+
 def test_predict_helpers_match_oracle(ctx):
     X, Y = port.synth(31, 500, 90, 3)
     st = port.fit(X, Y, 7, 0)
