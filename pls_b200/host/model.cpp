@@ -109,15 +109,42 @@ void Model::fit_on(DeviceMirror &data, const Mat2D &X, const Mat2D &Y, const MET
 }
 
 // ---- prediction helpers (pls.cpp:439-467) ---------------------------------------------------------
+// Rows of X_new are independent, so with several GPUs a large prediction is row-sharded like the fit (SURVEY
+// 8(f)-2): device i takes rows [b[i], b[i+1]) — its own share of the PCIe transfer and of the pass over X_new —
+// and the model (R, Q: K*A + M*A doubles) is simply handed to every device.  No communication.
+namespace {
+std::vector<int64_t> row_shards(Engine &e, int64_t rows) {
+    size_t g = e.ndev();
+    if (g < 2 || rows < e.shard_min_rows || rows < (int64_t)g) g = 1;
+    std::vector<int64_t> b(g + 1);
+    for (size_t i = 0; i <= g; ++i) b[i] = (int64_t)(i * (size_t)rows / g);
+    return b;
+}
+template <typename Fn>
+void over_shards(Engine &e, const std::vector<int64_t> &b, Fn fn) {
+    const size_t g = b.size() - 1;
+    if (g == 1) { fn(0); return; }
+    e.parallel([&](size_t i) { if (i < g) fn(i); });
+}
+}  // namespace
+
 const Mat2Dc Model::scores(const Mat2D &X_new, const size_t comp) const {
     assert(A >= comp);
     Engine &e = Engine::get();
     std::lock_guard<std::recursive_mutex> lk(e.mu);
     const Mat2D Rr = R.real();
     Mat2D S(X_new.rows(), comp);
-    if (comp > 0)
-        ok(plsb_scores(e.primary(), Rr.data(), Rr.rows(), (int64_t)comp, X_new.data(), ld(X_new), X_new.rows(), S.data()),
-           "plsb_scores");
+    if (comp > 0) {
+        const std::vector<int64_t> b = row_shards(e, X_new.rows());
+        std::vector<Mat2D> part(b.size() - 1);
+        over_shards(e, b, [&](size_t i) {
+            part[i].resize(b[i + 1] - b[i], comp);
+            ok(plsb_scores(e.ctx[i], Rr.data(), Rr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new), b[i + 1] - b[i],
+                           part[i].data()),
+               "plsb_scores");
+        });
+        for (size_t i = 0; i + 1 < b.size(); ++i) S.middleRows(b[i], b[i + 1] - b[i]) = part[i];
+    }
     return as_complex(S);
 }
 
@@ -147,10 +174,17 @@ const Mat2D Model::fitted_values(const Mat2D &X_new, const size_t comp) const {
     std::lock_guard<std::recursive_mutex> lk(e.mu);
     const Mat2D Rr = R.real(), Qr = Q.real();
     Mat2D F = Mat2D::Zero(X_new.rows(), Qr.rows());
-    if (comp > 0)
-        ok(plsb_fitted(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data(), ld(X_new),
-                       X_new.rows(), nullptr, 1, F.data()),
-           "plsb_fitted");
+    if (comp > 0) {
+        const std::vector<int64_t> b = row_shards(e, X_new.rows());
+        std::vector<Mat2D> part(b.size() - 1);
+        over_shards(e, b, [&](size_t i) {
+            part[i].resize(b[i + 1] - b[i], Qr.rows());
+            ok(plsb_fitted(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i],
+                           ld(X_new), b[i + 1] - b[i], nullptr, 1, part[i].data()),
+               "plsb_fitted");
+        });
+        for (size_t i = 0; i + 1 < b.size(); ++i) F.middleRows(b[i], b[i + 1] - b[i]) = part[i];
+    }
     return F;
 }
 
@@ -160,9 +194,15 @@ const Mat2D Model::residuals(const Mat2D &X_new, const Mat2D &Y_new, const size_
     std::lock_guard<std::recursive_mutex> lk(e.mu);
     const Mat2D Rr = R.real(), Qr = Q.real();
     Mat2D E(X_new.rows(), Qr.rows());
-    ok(plsb_fitted(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data(), ld(X_new),
-                   X_new.rows(), Y_new.data(), ld(Y_new), E.data()),
-       "plsb_fitted(residuals)");
+    const std::vector<int64_t> b = row_shards(e, X_new.rows());
+    std::vector<Mat2D> part(b.size() - 1);
+    over_shards(e, b, [&](size_t i) {
+        part[i].resize(b[i + 1] - b[i], Qr.rows());
+        ok(plsb_fitted(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new),
+                       b[i + 1] - b[i], Y_new.data() + b[i], ld(Y_new), part[i].data()),
+           "plsb_fitted(residuals)");
+    });
+    for (size_t i = 0; i + 1 < b.size(); ++i) E.middleRows(b[i], b[i + 1] - b[i]) = part[i];
     return E;
 }
 
@@ -171,10 +211,15 @@ const Row Model::SSE(const Mat2D &X_new, const Mat2D &Y_new, const size_t comp) 
     Engine &e = Engine::get();
     std::lock_guard<std::recursive_mutex> lk(e.mu);
     const Mat2D Rr = R.real(), Qr = Q.real();
-    Row sse(Qr.rows());
-    ok(plsb_sse(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data(), ld(X_new),
-                X_new.rows(), Y_new.data(), ld(Y_new), sse.data()),
-       "plsb_sse");
+    const std::vector<int64_t> b = row_shards(e, X_new.rows());
+    std::vector<Row> part(b.size() - 1, Row::Zero(Qr.rows()));
+    over_shards(e, b, [&](size_t i) {
+        ok(plsb_sse(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new),
+                    b[i + 1] - b[i], Y_new.data() + b[i], ld(Y_new), part[i].data()),
+           "plsb_sse");
+    });
+    Row sse = part[0];
+    for (size_t i = 1; i < part.size(); ++i) sse += part[i];   // shard order: deterministic
     return sse;
 }
 
@@ -241,9 +286,22 @@ Residual Model::cv_NEW_DATA(const Mat2D &X_new, const Mat2D &Y_new) const {
     const Mat2D Rr = R.real(), Qr = Q.real();
     const int64_t M = Y_new.cols(), rows = X_new.rows();
     std::vector<double> E((size_t)(M * (int64_t)A * rows));
-    ok(plsb_predict_residuals(e.primary(), Rr.data(), Qr.data(), Rr.rows(), M, (int64_t)A, X_new.data(), ld(X_new), rows,
-                              Y_new.data(), ld(Y_new), E.data()),
-       "plsb_predict_residuals");
+    const std::vector<int64_t> b = row_shards(e, rows);
+    if (b.size() == 2) {
+        ok(plsb_predict_residuals(e.primary(), Rr.data(), Qr.data(), Rr.rows(), M, (int64_t)A, X_new.data(), ld(X_new), rows,
+                                  Y_new.data(), ld(Y_new), E.data()),
+           "plsb_predict_residuals");
+    } else {
+        over_shards(e, b, [&](size_t i) {
+            const int64_t ri = b[i + 1] - b[i];
+            std::vector<double> Ei((size_t)(M * (int64_t)A * ri));
+            ok(plsb_predict_residuals(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), M, (int64_t)A, X_new.data() + b[i],
+                                      ld(X_new), ri, Y_new.data() + b[i], ld(Y_new), Ei.data()),
+               "plsb_predict_residuals");
+            for (int64_t mc = 0; mc < M * (int64_t)A; ++mc)   // column (m, c) of the block: rows [b[i], b[i+1])
+                std::copy(Ei.begin() + mc * ri, Ei.begin() + (mc + 1) * ri, E.begin() + mc * rows + b[i]);
+        });
+    }
     std::vector<Mat2D> Ev((size_t)M);
     for (int64_t m = 0; m < M; ++m)
         Ev[(size_t)m] = Eigen::Map<const Mat2D>(E.data() + (size_t)(m * (int64_t)A * rows), rows, (Eigen::Index)A);
@@ -258,10 +316,16 @@ void Model::print_explained_variance(const Mat2D &X, const Mat2D &Y, std::ostrea
     {
         std::lock_guard<std::recursive_mutex> lk(e.mu);
         const Mat2D Rr = R.real(), Qr = Q.real();
-        sse.resize(Qr.rows(), A);
-        ok(plsb_sse_prefixes(e.primary(), Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)A, X.data(), ld(X), X.rows(),
-                             Y.data(), ld(Y), sse.data()),
-           "plsb_sse_prefixes");
+        sse.setZero(Qr.rows(), A);
+        const std::vector<int64_t> b = row_shards(e, X.rows());
+        std::vector<Mat2D> part(b.size() - 1);
+        over_shards(e, b, [&](size_t i) {
+            part[i].resize(Qr.rows(), A);
+            ok(plsb_sse_prefixes(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)A, X.data() + b[i], ld(X),
+                                 b[i + 1] - b[i], Y.data() + b[i], ld(Y), part[i].data()),
+               "plsb_sse_prefixes");
+        });
+        for (const Mat2D &p : part) sse += p;
     }
     const Row sst = SST(Y);
     const size_t wd = ceil(std::log10(A));

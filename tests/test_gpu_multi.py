@@ -143,5 +143,9 @@ def test_cpp_layer_multi_gpu(tmp_path):
     for k in ("coef_A", "fitted_A", "sse"):
         assert relerr(many[k], one[k]) <= 1e-11, k
         assert relerr(many[k], g[k]) <= RTOL, k
+    # predictions are row-sharded over the GPUs too (scores, residuals, explained variance, cv_NEW_DATA)
+    for k in ("scores_A", "resid_A", "ev", "R"):
+        assert relerr(many[k], one[k]) <= 1e-11, k
+    assert relerr(stacked(many, "newdata", 3), stacked(one, "newdata", 3)) <= 1e-11
     assert np.array_equal(stacked(many, "lso", 3), stacked(one, "lso", 3))
     assert np.array_equal(stacked(many, "loo", 3), stacked(one, "loo", 3))
