@@ -68,6 +68,8 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double *__re
     __shared__ double sm[8][33];
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const int64_t i = (int64_t)blockIdx.x * 32 + tx;
+    pdl_wait();      // the partial rows come from the kernel before this one
+    pdl_launch();
     double acc = 0.0;
     if (i < len) {
         const double *p = part + i;
@@ -142,8 +144,8 @@ int launch_reduce_partials(plsb_ctx *c, const double *part, int64_t ld, int nb, 
     }
     {
         ProfScope ps(c, PLSB_PROF_REDUCE);
-        if (fused) reduce_partials_kernel<true><<<grid, 256, 0, c->stream>>>(part, ld, nb, len, out, x);
-        else reduce_partials_kernel<false><<<grid, 256, 0, c->stream>>>(part, ld, nb, len, out, x);
+        if (fused) PLSB_CUDA(launch_dep(reduce_partials_kernel<true>, dim3(grid), dim3(256), 0, c->stream, part, ld, nb, len, out, x));
+        else PLSB_CUDA(launch_dep(reduce_partials_kernel<false>, dim3(grid), dim3(256), 0, c->stream, part, ld, nb, len, out, x));
     }
     c->launches++;
     PLSB_CUDA(cudaGetLastError());

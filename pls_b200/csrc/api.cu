@@ -100,6 +100,11 @@ int dev_mem_available(plsb_ctx *c, size_t *bytes) {
     return PLSB_OK;
 }
 
+bool pdl_enabled() {
+    static const bool on = [] { const char *e = getenv("PLSB_NO_PDL"); return !(e && *e == '1'); }();
+    return on;
+}
+
 int ensure_part(plsb_ctx *c, size_t bytes) {
     if (bytes <= c->part_bytes) return PLSB_OK;
     if (c->part) {

@@ -141,6 +141,10 @@ __global__ void __launch_bounds__(NT) fused_pass_kernel(const PassArgs a) {
         }
     }
 
+    // X does not change during a fit: the first tiles are already in flight while the kernel that produces r
+    // (the step) is still running; everything below reads or overwrites data of the kernels before this one
+    pdl_wait();
+    pdl_launch();
     double rv[VEC], acc[VEC];
 #pragma unroll
     for (int v = 0; v < VEC / 2; ++v) {
@@ -502,7 +506,7 @@ static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, doubl
     PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     {
         ProfScope ps(c, PLSB_PROF_PASS_FUSED);
-        kern<<<(unsigned)grid, NT, smem, c->stream>>>(a);
+        PLSB_CUDA(launch_dep(kern, dim3((unsigned)grid), dim3(NT), smem, c->stream, a));
     }
     PLSB_CUDA(cudaGetLastError());
     c->launches += 1;

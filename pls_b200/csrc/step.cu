@@ -186,6 +186,11 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
         lv[j] = live[j] ? 1.0 : 0.0;
     }
     SC_TRACE(0);
+    // Launched as a programmatic dependent: the set-up below (pair table, S slice, barrier initialisation) overlaps
+    // the tail of the partial-row sum that produces g.  S is written only by the previous step, which completed
+    // before that kernel could trigger this launch — except for the initial step, whose S comes straight from
+    // the kernel before it.
+    if (s.a < 0) pdl_wait();
     for (int d = tid; d < npairs; d += SC_NT) {  // (u, v) of Gram entry d, u <= v
         int u = 0, rem = d;
         while (rem >= M - u) { rem -= M - u; ++u; }
@@ -198,6 +203,8 @@ __global__ void __launch_bounds__(SC_NT, 1) step_cluster_kernel(const StepArgs s
             for (int m = 0; m < M; ++m) sm.S[(size_t)m * cpc + kl[j]] = s.S[(size_t)m * ldk + kg[j]];
     __syncthreads();  // pair table visible (each thread touches only its own columns of sm.S)
     cluster_barrier();  // every CTA's mbarriers are initialised before any remote traffic can reach them
+    pdl_wait();
+    pdl_launch();
     SC_TRACE(1);
     const int an = s.a + 1;
     double x[SC_KPT];  // r_a, later w
@@ -333,13 +340,15 @@ static int launch_step_cluster(plsb_ctx *c, const StepArgs &s) {
     cfg.blockDim = dim3(SC_NT);
     cfg.dynamicSmemBytes = lay.bytes;
     cfg.stream = c->stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = SC_NCTA;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     if (getenv("PLSB_STEP_TRACE")) {  // dev tool (tools/steptrace.py): phase timestamps of this launch on stderr
         static long long *tr = nullptr;
         if (!tr) PLSB_CUDA(cudaMalloc(&tr, 16 * sizeof(long long)));
