@@ -398,6 +398,16 @@ def run_ours(args):
             cpu = {"value": 1.0 / (sec * N / args.cpu_sample), "unit": "fits/s", "cores": cores, "kind": kind,
                    "sample": f"one KERNEL_TYPE1 fit (A=32) on the first {args.cpu_sample} rows of the C4 matrix "
                              f"({sec:.2f} s), scaled by N/{args.cpu_sample}"}
+            try:    # the reference built with -fopenmp (Eigen threads GEMM only): all cores, a 20000-row sample
+                from oracle import port, ref
+                Xo, Yo = port.synth(C4["seed"], 20000, K, M, L=C4["L"])
+                t1, t2 = ref.time_fit_omp(Xo, Yo, A, 0, 1), ref.time_fit_omp(Xo, Yo, A, 1, 1)
+                if t1 is not None:
+                    cpu["openmp_build"] = {"cores": os.cpu_count(), "type1_fits_per_s": 1.0 / (t1 * N / 20000),
+                                           "type2_fits_per_s": 1.0 / (t2 * N / 20000),
+                                           "sample": f"20000 rows, type 1 {t1:.2f} s, type 2 {t2:.2f} s, scaled by N/20000"}
+            except Exception as e:
+                cpu["openmp_build"] = {"error": repr(e)}
         except Exception as e:  # the oracle always exists; report rather than hide a failure
             cpu = {"error": repr(e)}
 

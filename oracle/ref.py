@@ -215,3 +215,21 @@ def time_fit(X, Y, A, method=0, reps=1):
     X, Y = F(X), F(Y)
     return lib().plsref_time_fit(P(X), i64(X.shape[0]), i64(X.shape[1]), P(Y), i64(Y.shape[1]), C.c_int(method),
                                  i64(A), C.c_int(reps))
+
+
+_SO_OMP = os.path.join(_HERE, "_ref", "libplsref_omp.so")
+_lib_omp = None
+
+
+def time_fit_omp(X, Y, A, method=0, reps=1):
+    """time_fit on the -fopenmp build of the same reference sources (Eigen threads its GEMM kernels only);
+    None when that build is absent."""
+    global _lib_omp
+    if _lib_omp is None:
+        if not os.path.exists(_SO_OMP):
+            return None
+        _lib_omp = C.CDLL(_SO_OMP)
+        _lib_omp.plsref_time_fit.restype = C.c_double
+    X, Y = F(X), F(Y)
+    return _lib_omp.plsref_time_fit(P(X), i64(X.shape[0]), i64(X.shape[1]), P(Y), i64(Y.shape[1]), C.c_int(method),
+                                    i64(A), C.c_int(reps))
