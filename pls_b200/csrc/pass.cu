@@ -91,6 +91,11 @@ struct PassArgs {
     int64_t N, tiles;
     int ldk, ldm, ldp, stages;
     int m0, mc;        // xty: responses [m0, m0+mc)
+    // fused pass: the tiles are dealt to `vgrid` VIRTUAL CTAs (virtual CTA p owns tiles p, p + vgrid, ... and partial
+    // row p); a physical CTA runs virtual CTAs blockIdx.x, blockIdx.x + gridDim.x, ... one after the other.  The sums
+    // therefore do not depend on how many CTAs share an SM (1 with a deep ring or 2 with a shallow one — tuned at run
+    // time, see launch_fused_pass): results stay bit-identical across configurations.
+    int vgrid;
 };
 
 // Thread layout: NT threads = G row groups x TPR threads per row.  A tile has ROWS = G*RB rows; group g
@@ -134,9 +139,10 @@ __global__ void __launch_bounds__(NT) fused_pass_kernel(const PassArgs a) {
         mbar_fence_init();
     }
     __syncthreads();
+    int j = 0;                 // tiles consumed so far by this CTA (all virtual CTAs): stage j % stages, parity from j / stages
     if (tid == 0) {
         for (int s = 0; s < a.stages; ++s) {
-            int64_t tile = (int64_t)blockIdx.x + (int64_t)s * gridDim.x;
+            int64_t tile = (int64_t)blockIdx.x + (int64_t)s * a.vgrid;
             if (tile < a.tiles) issue_tile(a, tile, C::ROWS, stage0 + (size_t)s * tile_bytes, nullptr, &full[s], false);
         }
     }
@@ -156,13 +162,24 @@ __global__ void __launch_bounds__(NT) fused_pass_kernel(const PassArgs a) {
             rv[2 * v] = 0.0;
             rv[2 * v + 1] = 0.0;
         }
-        acc[2 * v] = 0.0;
-        acc[2 * v + 1] = 0.0;
     }
+
+    for (int vb = blockIdx.x; vb < a.vgrid; vb += gridDim.x) {
+    if (vb != (int)blockIdx.x) {
+        __syncthreads();       // the previous virtual CTA is done with the ring and the reduction scratch
+        if (tid == 0) {
+            for (int s = 0; s < a.stages; ++s) {
+                int64_t tile = (int64_t)vb + (int64_t)s * a.vgrid;
+                const int slot = (j + s) % a.stages;
+                if (tile < a.tiles) issue_tile(a, tile, C::ROWS, stage0 + (size_t)slot * tile_bytes, nullptr, &full[slot], false);
+            }
+        }
+    }
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) acc[v] = 0.0;
     double tt = 0.0;
 
-    int j = 0;
-    for (int64_t tile = blockIdx.x; tile < a.tiles; tile += gridDim.x, ++j) {
+    for (int64_t tile = vb; tile < a.tiles; tile += a.vgrid, ++j) {
         const int s = j % a.stages;
         const uint32_t parity = (uint32_t)((j / a.stages) & 1);
         const int64_t row0 = tile * C::ROWS + (int64_t)g * RB;
@@ -209,7 +226,7 @@ __global__ void __launch_bounds__(NT) fused_pass_kernel(const PassArgs a) {
             }
         }
         if (tid == 0) {
-            const int64_t next = tile + (int64_t)a.stages * gridDim.x;
+            const int64_t next = tile + (int64_t)a.stages * a.vgrid;
             if (next < a.tiles) issue_tile(a, next, C::ROWS, stage0 + (size_t)s * tile_bytes, nullptr, &full[s], false);
         }
         // g += x * t ; tt += t^2 ; T(:,a) = t
@@ -227,8 +244,8 @@ __global__ void __launch_bounds__(NT) fused_pass_kernel(const PassArgs a) {
         }
     }
 
-    // cross-group reduction inside the CTA, then one partial row per CTA
-    double *prow = a.part + (size_t)blockIdx.x * a.ldp;
+    // cross-group reduction inside the CTA, then one partial row per virtual CTA
+    double *prow = a.part + (size_t)vb * a.ldp;
     if (C::G == 1) {
 #pragma unroll
         for (int v = 0; v < VEC / 2; ++v) {
@@ -260,6 +277,7 @@ __global__ void __launch_bounds__(NT) fused_pass_kernel(const PassArgs a) {
             prow[a.ldk] = s;
         }
     }
+    }   // virtual CTAs
 }
 
 // S partials: acc[m][v] += x[v] * y[m] for the mc (<= MC) responses starting at m0
@@ -474,8 +492,10 @@ static int run_wide_xty(plsb_ctx *c, const plsb_dataset *ds, double *S) {
     return PLSB_OK;
 }
 
+// One launch of the fused pass with `ctas_per_sm` resident CTAs per SM (0: the default for this shape).
 template <int NT, int TPR, int VEC, int RB>
-static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
+static int launch_fused_cfg(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *t_out, int ctas_per_sm,
+                            int *vgrid_out, int *ldp_out) {
     using C = PassCfg<NT, TPR, VEC, RB>;
     PassArgs a{};
     a.X = ds->X; a.r = r; a.t_out = t_out; a.N = ds->N; a.ldk = (int)ds->ldk; a.ldp = (int)ds->ldk + 2;
@@ -483,24 +503,29 @@ static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, doubl
     const size_t tile_bytes = (size_t)C::ROWS * a.ldk * 8;
     const size_t tail = 64 + sizeof(double) * ((size_t)2 * C::NW * RB > (size_t)C::G * a.ldk + C::G
                                                    ? (size_t)2 * C::NW * RB : (size_t)C::G * a.ldk + C::G) + 128;
-    int ctas_per_sm = env_int("PLSB_PASS_CTAS_PER_SM", NT >= 512 ? 1 : 2);
+    const int vper = NT >= 512 ? 1 : 2;                       // virtual CTAs per SM: fixes the summation order
+    if (ctas_per_sm <= 0) ctas_per_sm = env_int("PLSB_PASS_CTAS_PER_SM", vper);
+    if (ctas_per_sm > vper) ctas_per_sm = vper;
     size_t budget = (c->smem_optin - 1024) / ctas_per_sm;
     if (budget > c->smem_optin) budget = c->smem_optin;
-    int stages = (int)((budget - tail) / tile_bytes);
+    int stages = budget > tail ? (int)((budget - tail) / tile_bytes) : 0;
     if (stages > env_int("PLSB_PASS_STAGES", 4)) stages = env_int("PLSB_PASS_STAGES", 4);
     if (stages > 8) stages = 8;
     if (stages < 1) {  // tile does not fit next to a second CTA: take the whole SM
         ctas_per_sm = 1;
-        stages = (int)((c->smem_optin - tail) / tile_bytes);
+        stages = c->smem_optin > tail ? (int)((c->smem_optin - tail) / tile_bytes) : 0;
         if (stages > 8) stages = 8;
         if (stages < 1) { set_error("fused pass: K=%lld does not fit shared memory", (long long)ds->K); return PLSB_ERR_UNSUPPORTED; }
     }
     a.stages = stages;
     const size_t smem = (size_t)stages * tile_bytes + tail;
+    int64_t vgrid = (int64_t)c->sm_count * vper;
+    if (vgrid > a.tiles) vgrid = a.tiles;
+    if (vgrid < 1) vgrid = 1;
+    a.vgrid = (int)vgrid;
     int64_t grid = (int64_t)c->sm_count * ctas_per_sm;
-    if (grid > a.tiles) grid = a.tiles;
-    if (grid < 1) grid = 1;
-    PLSB_TRY(ensure_part(c, (size_t)grid * a.ldp * sizeof(double)));
+    if (grid > vgrid) grid = vgrid;
+    PLSB_TRY(ensure_part(c, (size_t)vgrid * a.ldp * sizeof(double)));
     a.part = c->part;
     auto kern = fused_pass_kernel<NT, TPR, VEC, RB>;
     PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -510,7 +535,28 @@ static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, doubl
     }
     PLSB_CUDA(cudaGetLastError());
     c->launches += 1;
-    return launch_reduce_partials(c, c->part, a.ldp, (int)grid, a.ldk + 1, out, across_ranks);
+    *vgrid_out = (int)vgrid; *ldp_out = a.ldp;
+    return PLSB_OK;
+}
+
+// Which occupancy streams faster — two CTAs per SM with a one-tile ring each, or one CTA with a three-tile ring —
+// depends on the SM clock the board sustains under its power cap: two win by ~1 % at 1.73 GHz, one wins by 2-3.5 %
+// at the ~1.5 GHz these boards settle at under a sustained FP64 stream (one CTA re-arms its ring sooner after a tile
+// has been consumed, so it is less sensitive to how long the arithmetic takes).  A timing probe at the first fit
+// sees the un-capped clock and picks the wrong one, so large streams simply take the deep ring.  The choice cannot
+// change the results (virtual CTAs); PLSB_PASS_CTAS_PER_SM overrides it.
+template <int NT, int TPR, int VEC, int RB>
+static int tuned_ctas(plsb_ctx *, const plsb_dataset *ds, const double *) {
+    if (NT >= 512 || getenv("PLSB_PASS_CTAS_PER_SM") || ds->N * ds->ldk < ((int64_t)1 << 27)) return 0;
+    return 1;
+}
+
+template <int NT, int TPR, int VEC, int RB>
+static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
+    int vgrid = 0, ldp = 0;
+    const int ctas = tuned_ctas<NT, TPR, VEC, RB>(c, ds, r);
+    PLSB_TRY((launch_fused_cfg<NT, TPR, VEC, RB>(c, ds, r, t_out, ctas, &vgrid, &ldp)));
+    return launch_reduce_partials(c, c->part, ldp, vgrid, ds->ldk + 1, out, across_ranks);
 }
 
 int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
