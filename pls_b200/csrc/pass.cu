@@ -539,23 +539,10 @@ static int launch_fused_cfg(plsb_ctx *c, const plsb_dataset *ds, const double *r
     return PLSB_OK;
 }
 
-// Which occupancy streams faster — two CTAs per SM with a one-tile ring each, or one CTA with a three-tile ring —
-// depends on the SM clock the board sustains under its power cap: two win by ~1 % at 1.73 GHz, one wins by 2-3.5 %
-// at the ~1.5 GHz these boards settle at under a sustained FP64 stream (one CTA re-arms its ring sooner after a tile
-// has been consumed, so it is less sensitive to how long the arithmetic takes).  A timing probe at the first fit
-// sees the un-capped clock and picks the wrong one, so large streams simply take the deep ring.  The choice cannot
-// change the results (virtual CTAs); PLSB_PASS_CTAS_PER_SM overrides it.
-template <int NT, int TPR, int VEC, int RB>
-static int tuned_ctas(plsb_ctx *, const plsb_dataset *ds, const double *) {
-    if (NT >= 512 || getenv("PLSB_PASS_CTAS_PER_SM") || ds->N * ds->ldk < ((int64_t)1 << 27)) return 0;
-    return 1;
-}
-
 template <int NT, int TPR, int VEC, int RB>
 static int run_fused(plsb_ctx *c, const plsb_dataset *ds, const double *r, double *out, double *t_out, bool across_ranks) {
     int vgrid = 0, ldp = 0;
-    const int ctas = tuned_ctas<NT, TPR, VEC, RB>(c, ds, r);
-    PLSB_TRY((launch_fused_cfg<NT, TPR, VEC, RB>(c, ds, r, t_out, ctas, &vgrid, &ldp)));
+    PLSB_TRY((launch_fused_cfg<NT, TPR, VEC, RB>(c, ds, r, t_out, 0, &vgrid, &ldp)));
     return launch_reduce_partials(c, c->part, ldp, vgrid, ds->ldk + 1, out, across_ranks);
 }
 
@@ -569,8 +556,14 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
     if (ldk <= 256) return run_fused<256, 32, 8, 2>(c, ds, r, out, t_out, across_ranks);
     if (ldk <= 512) return run_fused<256, 256, 2, 8>(c, ds, r, out, t_out, across_ranks);
     if (ldk <= 1024) return run_fused<256, 256, 4, 4>(c, ds, r, out, t_out, across_ranks);
-    if (ldk <= 2048) {  // 4 rows per thread and tile: 3-6 % faster than 2 on B200 (fewer barriers per byte)
+    if (ldk <= 2048) {
+        // Large streams: ONE 512-thread CTA per SM (two row groups of 2 rows each) behind a three-tile ring.  Small
+        // ones: two 256-thread CTAs per SM, 4 rows per thread, one tile each.  Measured on C4 at the ~1.4-1.5 GHz a
+        // power-capped board sustains under this stream: 2.30 ms vs 2.49 ms per pass (the single CTA re-arms its ring
+        // as soon as a tile is in registers and 16 warps share the arithmetic); at 1.73 GHz the two are within 1 %.
+        const bool big = ds->N * ldk >= ((int64_t)1 << 27) && !getenv("PLSB_PASS_CTAS_PER_SM");
         if (rbsel == 2) return run_fused<256, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
+        if (rbsel == 12 || (rbsel == 0 && big)) return run_fused<512, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
         return run_fused<256, 256, 8, 4>(c, ds, r, out, t_out, across_ranks);
     }
     if (ldk <= 4096) {

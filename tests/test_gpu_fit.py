@@ -154,6 +154,13 @@ def test_pass_occupancy_does_not_change_the_bits(ctx, N, K, monkeypatch):
     monkeypatch.setenv("PLSB_PASS_STAGES", "2")
     c = ds.fit(6, 0)
     assert all(np.array_equal(a[k], b[k]) and np.array_equal(a[k], c[k]) for k in "WPRQT")
+    if K > 1024:   # the large-stream configuration (one 512-thread CTA per SM, two row groups), forced on a small shape
+        monkeypatch.delenv("PLSB_PASS_CTAS_PER_SM"); monkeypatch.delenv("PLSB_PASS_STAGES")
+        monkeypatch.setenv("PLSB_PASS_RB", "12")
+        d = ds.fit(6, 0)
+        assert_state_close(d, a, rtol=1e-11)
+        X, Y = ds.download()
+        assert_state_close(d, port.fit(X, Y, 6, 0), rtol=1e-8)
     ds.close()
 
 
