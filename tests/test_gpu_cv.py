@@ -78,7 +78,10 @@ def test_c5s_loo(ctx):
 
 
 @pytest.mark.parametrize("N,K,M,A,ts,nf", [(45, 11, 2, 5, 9, 30), (200, 77, 1, 6, 1, 200), (120, 300, 3, 5, 40, 7),
-                                           (64, 130, 8, 4, 3, 50), (700, 20, 2, 4, 300, 3)])
+                                           (64, 130, 8, 4, 3, 50), (700, 20, 2, 4, 300, 3),
+                                           # K >= 1024: the fused per-component fold kernel, every M variant
+                                           (90, 1100, 3, 5, 1, 40), (60, 2049, 1, 4, 7, 12), (50, 4096, 8, 4, 2, 9),
+                                           (70, 1024, 2, 6, 20, 6), (40, 1500, 5, 9, 1, 40)])
 def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
     X, Y = port.synth(500 + N + K, N, K, M, L=max(A, 4))
     rng = np.random.default_rng(N)
