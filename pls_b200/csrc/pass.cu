@@ -561,7 +561,10 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
         // ones: two 256-thread CTAs per SM, 4 rows per thread, one tile each.  Measured on C4 at the ~1.4-1.5 GHz a
         // power-capped board sustains under this stream: 2.30 ms vs 2.49 ms per pass (the single CTA re-arms its ring
         // as soon as a tile is in registers and 16 warps share the arithmetic); at 1.73 GHz the two are within 1 %.
-        const bool big = ds->N * ldk >= ((int64_t)1 << 27) && !getenv("PLSB_PASS_CTAS_PER_SM");
+        // (Row shards of a multi-GPU fit are smaller, spend a larger share of the time in the latency-bound kernels
+        // between the passes and keep a higher clock: measured at 4 GB and 2 GB per GPU the two-CTA shape is 6-8 %
+        // faster, at 8 GB and 16 GB the one-CTA shape is 3-7 % faster — hence the size threshold.)
+        const bool big = ds->N * ldk >= 3 * ((int64_t)1 << 28) && !getenv("PLSB_PASS_CTAS_PER_SM");
         if (rbsel == 2) return run_fused<256, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
         if (rbsel == 12 || (rbsel == 0 && big)) return run_fused<512, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
         return run_fused<256, 256, 8, 4>(c, ds, r, out, t_out, across_ranks);
