@@ -229,8 +229,9 @@ def run_ours(args):
     # ---- device-resident timing: K steps bracketed by barrier + sync; per-kernel CUDA events inside ----
     for _ in range(max(args.warmup, 3)):
         ds.fit_nocopy(A, 0)
-    # (1) the timed region: exactly K fits, nothing but the product's own launches on the stream
-    ctx.profile(False)
+    # (1) the timed region: exactly K fits; one CUDA event pair per fit on the library's stream (device time), no
+    # event between the kernels of a fit
+    ctx.profile(2); ctx.profile_reset()
     barrier()
     l0 = ctx.launch_count()
     t0 = time.perf_counter()
@@ -239,6 +240,7 @@ def run_ours(args):
     barrier()
     wall = time.perf_counter() - t0
     launches = ctx.launch_count() - l0
+    dev_timed_ms, n_timed = ctx.profile_get("fit_total")
     # (2) the same K fits again with a CUDA event pair around every launch (library stream): per-kernel durations
     # for the roofline.  Kept out of (1) because an event record between two kernels switches off the programmatic
     # dependent launch that lets a kernel's set-up overlap its predecessor's tail.
@@ -256,7 +258,8 @@ def run_ours(args):
     step_ms, nstep = ctx.profile_get("step")
     red_ms, nred = ctx.profile_get("reduce")
     ctx.profile(False)
-    ms_per_step = wall * 1e3 / args.steps
+    # device time of the K fits (CUDA events) and the host clock around the bracketed region: report the larger
+    ms_per_step = max(wall * 1e3 / args.steps, dev_timed_ms / max(n_timed, 1))
     if dist is not None:
         t = torch.tensor([ms_per_step, wall_instr * 1e3 / args.steps, pass_ms / max(npass, 1)], device="cuda", dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -427,6 +430,7 @@ def run_ours(args):
                 "config": {"workload": WORKLOAD, "parallelism": f"rows sharded over {world} rank(s)",
                            "l2": "inputs (16.4 GB of X per fit pass) are larger than L2; no flush needed"},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "cv": cv, "cv_small": cv_small, "xtx_c4": xtx, "gpu_launches": int(launches), "clocks": clocks,
+                "device_ms_per_step": dev_timed_ms / max(n_timed, 1),
                 "instrumented": {"ms_per_step": instr_ms, "device_ms_per_fit": dev_ms / max(nfit, 1),
                                  "what": "the same K fits repeated with a CUDA event pair around every launch: source of the per-kernel times"}}
         print(json.dumps(line), flush=True)

@@ -157,6 +157,8 @@ int plsb_lso_folds(int64_t N, double test_fraction, int64_t num_trials, uint32_t
 #define PLSB_PROF_REDUCE 8      /* cross-CTA partial-row sums after a pass */
 #define PLSB_PROF_SCORES 9      /* DMMA scores S = X R */
 #define PLSB_PROF_NSLOTS 10
+/* on: 0 off; 1 a CUDA event pair around every launch group; 2 only around whole fits (device time of a fit without
+ * an event between its kernels, which would switch off their programmatic dependent launch) */
 int plsb_profile_enable(plsb_ctx_t ctx, int on);
 int plsb_profile_reset(plsb_ctx_t ctx);
 /* total milliseconds and launch count accumulated in a slot since the last reset */

@@ -109,7 +109,8 @@ class Context:
 
     # -- profiling -----------------------------------------------------------------------------
     def profile(self, on=True):
-        check(lib().plsb_profile_enable(self.h, C.c_int(1 if on else 0)))
+        """on: False/0 off, True/1 events around every launch group, 2 only around whole fits"""
+        check(lib().plsb_profile_enable(self.h, C.c_int(2 if on == 2 else (1 if on else 0))))
 
     def profile_reset(self):
         check(lib().plsb_profile_reset(self.h))

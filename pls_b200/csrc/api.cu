@@ -119,7 +119,7 @@ int ensure_part(plsb_ctx *c, size_t bytes) {
 }
 
 ProfScope::ProfScope(plsb_ctx *ctx, int slot) : c(ctx) {
-    if (!c->prof) return;
+    if (!c->prof || (c->prof == 2 && slot != PLSB_PROF_FIT_TOTAL)) return;
     plsb_ctx::Pending p;
     p.slot = slot;
     for (cudaEvent_t *e : {&p.a, &p.b}) {
@@ -260,7 +260,7 @@ int plsb_comm_init(plsb_ctx_t c, int rank, int nranks, const void *id128) {
 int plsb_profile_enable(plsb_ctx_t c, int on) {
     PLSB_ARG(c, "ctx is null");
     PLSB_TRY(prof_drain(c));
-    c->prof = on != 0;
+    c->prof = on == 2 ? 2 : (on != 0 ? 1 : 0);
     return PLSB_OK;
 }
 int plsb_profile_reset(plsb_ctx_t c) {

@@ -30,7 +30,7 @@ struct plsb_ctx {
         unsigned long long seq = 0;     // exchanges done so far (identical on every rank)
     } xchg;
     // profiling
-    bool prof = false;
+    int prof = 0;   // 0 off, 1 an event pair around every launch group, 2 only around whole fits (PLSB_PROF_FIT_TOTAL)
     struct Pending { int slot; cudaEvent_t a, b; };
     std::vector<Pending> pending;
     std::vector<cudaEvent_t> pool;
