@@ -207,7 +207,9 @@ def run_ours(args):
     ctx = _capi.Context(local)
     # nvidia-smi needs up to a second to come up when several ranks start one each: start sampling now, keep only the
     # samples of the timed region (ClockSampler.finish)
-    sampler = ClockSampler(local); sampler.start()
+    sampler = ClockSampler(local)
+    if rank == 0:      # one poller per job: the line rank 0 prints carries its GPU's clocks
+        sampler.start()
     if world > 1:
         uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
         if rank == 0:
@@ -251,7 +253,7 @@ def run_ours(args):
         ds.fit_nocopy(A, 0)
     barrier()
     wall_instr = time.perf_counter() - t1
-    clocks = sampler.finish(since=t0)
+    clocks = sampler.finish(since=t0) if rank == 0 else None
     dev_ms, nfit = ctx.profile_get("fit_total")
     pass_ms, npass = ctx.profile_get("pass_fused")
     xty_ms, nxty = ctx.profile_get("pass_xty")
