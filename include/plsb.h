@@ -56,7 +56,10 @@ int plsb_comm_init(plsb_ctx_t ctx, int rank, int nranks, const void *id128);
 int plsb_comm_allreduce_test(plsb_ctx_t ctx, double *host_buf, int64_t n);
 
 /* ---- datasets: Model's `_X,_Y` copy (pls.cpp:344) becomes a device-resident mirror ---------- */
-/* X: N x K, Y: N x M host column-major (pinned or pageable).  Rows are this rank's shard. */
+/* X: N x K, Y: N x M host column-major (pinned or pageable).  Rows are this rank's shard.
+ * The transfer is PCIe-bound; for tall matrices (256 <= K <= 3072, N >= max(16 K, 65536); PLSB_UPLOAD_GRAM=0/1
+ * overrides) the rows go up in blocks and XX = X'X, XY = X'Y (pls.cpp:396-398) are accumulated on the FP64 tensor
+ * cores while the next block is in flight; the data set then carries them and plsb_fit runs from them. */
 int plsb_dataset_create(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K,
                         const double *Y, int64_t ldy, int64_t M, plsb_dataset_t *ds);
 /* Same, but X / Y are DEVICE pointers (column-major) on ctx's device. */
@@ -75,7 +78,12 @@ int plsb_dataset_set_sharded(plsb_dataset_t ds, int sharded);
 
 /* ---- fit: Model::plsr (pls.cpp:390-437) ------------------------------------------------------ */
 /* Outputs (host, column-major, real parts; the reference's complex members have zero imaginary
- * part): W,P,R are K x A, Q is M x A, T is N x A (this rank's rows; KERNEL_TYPE1 only; may be NULL). */
+ * part): W,P,R are K x A, Q is M x A, T is N x A (this rank's rows; KERNEL_TYPE1 only; may be NULL).
+ * `method` selects the reference's kernel (pls.cpp:419-424): KERNEL_TYPE1 streams X once per component,
+ * KERNEL_TYPE2 builds X'X first.  A data set that already carries X'X (see plsb_dataset_create) is fitted from it
+ * whatever `method` says — the same model (both kernels sit at the same distance from the reference's result,
+ * profiles/r1c_fullsize_parity.json) — and T, when asked for, comes from one extra pass T = X R;
+ * PLSB_FIT_NO_GRAM=1 forces the streaming passes.  T in pinned memory is sent home while the fit is still running. */
 int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, double *R, double *Q,
              double *T);
 /* One-shot form taking host matrices (upload + fit), the shape Model's constructor has (pls.cpp:340-353). */
