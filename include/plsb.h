@@ -36,6 +36,7 @@ extern "C" {
 
 typedef struct plsb_ctx *plsb_ctx_t;         /* one device (+ optional communicator) */
 typedef struct plsb_dataset *plsb_dataset_t; /* device-resident X, Y (row shard of this rank) */
+typedef struct plsb_model *plsb_model_t;     /* device-resident fit results W, P, R, Q, T */
 
 /* ---- context ------------------------------------------------------------------------------- */
 const char *plsb_last_error(void);
@@ -86,6 +87,13 @@ int plsb_dataset_set_sharded(plsb_dataset_t ds, int sharded);
  * PLSB_FIT_NO_GRAM=1 forces the streaming passes.  T in pinned memory is sent home while the fit is still running. */
 int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, double *R, double *Q,
              double *T);
+/* The same fit with every result FORMED AND KEPT IN HBM (W, P, R, Q and — KERNEL_TYPE1, like the reference,
+ * pls.cpp:394/434 — the N x A scores T of this rank's rows): nothing crosses PCIe until plsb_model_download asks
+ * for it (any output pointer may be NULL).  What a caller that only wants a few of the matrices, or repeated fits
+ * (bench.py's device-resident figure), uses. */
+int plsb_fit_resident(plsb_dataset_t ds, int64_t A, int method, plsb_model_t *model);
+int plsb_model_download(plsb_model_t model, double *W, double *P, double *R, double *Q, double *T);
+int plsb_model_destroy(plsb_model_t model);
 /* One-shot form taking host matrices (upload + fit), the shape Model's constructor has (pls.cpp:340-353). */
 int plsb_fit_host(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K, const double *Y,
                   int64_t ldy, int64_t M, int64_t A, int method, double *W, double *P, double *R,
@@ -128,6 +136,16 @@ int plsb_sse(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_
  * test_size rows per (m, c) column and only this call's rows are written. */
 int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
                   const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E);
+/* Same folds, with validation's PRESS sums (pls.cpp:235-252: column sums of squared residuals) reduced ON THE DEVICE:
+ * press[(c-1)*M + m] (M x A column-major) = sum over THIS CALL's folds and held-out rows of E[m][row][c]^2 (fixed-order
+ * reduction, no atomics; fold shards add their partial matrices in shard order, MSE = sum / rows_total).  E may be
+ * NULL: then the residual block never leaves the device (LOO on 1M x 2048 would ship M*A*N*8 = 2 GB per call).
+ * optimal_num_components (pls.cpp:265-289) ranks individual residuals (Wilcoxon) and therefore still needs E.
+ * Data sets small enough for one SM's shared memory (N*K*8 <~ 200 KB: the reference's nir / toy files) run as ONE
+ * launch, each CTA fitting whole folds with the KERNEL_TYPE1 recurrence; larger ones use Gram downdates + one
+ * batched DMMA GEMM per component (PLSB_CV_NO_SMALL=1 forces the latter). */
+int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
+                        const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E, double *press);
 
 /* ---- column statistics and z-scoring on the device: SST (pls.cpp:69-77), colwise_stdev (79-87),
  * colwise_z_scores (93-111) — the CLI's pre-processing (main.cpp:24-25).  Two-pass formulas like the reference;

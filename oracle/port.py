@@ -61,6 +61,28 @@ def fit(X, Y, A, method=0, want_T=True):
     return dict(W=W, P=Pm, R=R, Q=Q, T=T)
 
 
+_lib_ext = None
+
+
+def fit_ext(X, Y, A, want_T=True):
+    """The KERNEL_TYPE1 fit in x87 extended precision (oracle/pls_oracle_ext.c): yardstick for FP64 rounding error."""
+    global _lib_ext
+    if _lib_ext is None:
+        so = os.path.join(_HERE, "liboracle_ext.so")
+        if not os.path.exists(so):
+            subprocess.check_call(["make", "-C", _HERE, "liboracle_ext.so"], stdout=subprocess.DEVNULL)
+        _lib_ext = C.CDLL(so)
+    X, Y = F(X), F(Y)
+    N, K = X.shape
+    M = Y.shape[1]
+    W = np.zeros((K, A), order="F"); Pm = np.zeros((K, A), order="F")
+    R = np.zeros((K, A), order="F"); Q = np.zeros((M, A), order="F")
+    T = np.zeros((N, A), order="F") if want_T else None
+    _lib_ext.orc_fit_ext(P(X), i64(N), i64(K), P(Y), i64(M), i64(A), P(W), P(Pm), P(R), P(Q),
+                         P(T) if T is not None else None)
+    return dict(W=W, P=Pm, R=R, Q=Q, T=T)
+
+
 def coefficients(R, Q, comp):
     R, Q = F(R), F(Q)
     K, M = R.shape[0], Q.shape[0]

@@ -50,82 +50,86 @@ def lib():
 class Model:
     """PLS::Model(X, Y, method, A) of the reference (pls.h:187-191)."""
 
-    def __init__(self, X, Y, A, method=0):
+    def __init__(self, X, Y, A, method=0, omp=False):
+        """omp=True drives the -fopenmp build of the same sources (Eigen threads its GEMM kernels only)."""
         self.X, self.Y = F(X), F(Y)
         self.N, self.K = self.X.shape
         self.M = self.Y.shape[1]
         self.A, self.method = A, method
-        self.h = C.c_void_p(lib().plsref_model_new(P(self.X), i64(self.N), i64(self.K), P(self.Y), i64(self.M),
-                                                   C.c_int(method), i64(A)))
+        self._lib = lib_omp() if omp else lib()
+        self.h = C.c_void_p(self._lib.plsref_model_new(P(self.X), i64(self.N), i64(self.K), P(self.Y), i64(self.M),
+                                                       C.c_int(method), i64(A)))
 
-    def __del__(self):
+    def close(self):
         if getattr(self, "h", None):
-            lib().plsref_model_free(self.h)
+            self._lib.plsref_model_free(self.h)
             self.h = None
+
+    __del__ = close
 
     def state(self):
         K, M, A, N = self.K, self.M, self.A, self.N
         W = np.zeros((K, A), order="F"); Pm = np.zeros((K, A), order="F")
         R = np.zeros((K, A), order="F"); Q = np.zeros((M, A), order="F")
         T = np.zeros((N, A), order="F") if self.method == 0 else None
-        lib().plsref_model_state(self.h, P(W), P(Pm), P(R), P(Q), P(T) if T is not None else None)
+        self._lib.plsref_model_state(self.h, P(W), P(Pm), P(R), P(Q), P(T) if T is not None else None)
         return dict(W=W, P=Pm, R=R, Q=Q, T=T)
 
     def max_imag(self):
-        return lib().plsref_model_max_imag(self.h)
+        return self._lib.plsref_model_max_imag(self.h)
 
     def scores(self, Xn, comp):
         Xn = F(Xn)
         S = np.zeros((Xn.shape[0], comp), order="F")
-        lib().plsref_scores(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), i64(comp), P(S))
+        self._lib.plsref_scores(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), i64(comp), P(S))
         return S
 
     def coefficients(self, comp):
         B = np.zeros((self.K, self.M), order="F")
-        lib().plsref_coefficients(self.h, i64(comp), P(B))
+        self._lib.plsref_coefficients(self.h, i64(comp), P(B))
         return B
 
     def fitted_values(self, Xn, comp):
         Xn = F(Xn)
         Fv = np.zeros((Xn.shape[0], self.M), order="F")
-        lib().plsref_fitted_values(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), i64(self.M), i64(comp), P(Fv))
+        self._lib.plsref_fitted_values(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), i64(self.M), i64(comp), P(Fv))
         return Fv
 
     def residuals(self, Xn, Yn, comp):
         Xn, Yn = F(Xn), F(Yn)
         E = np.zeros(Yn.shape, order="F")
-        lib().plsref_residuals(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), i64(comp), P(E))
+        self._lib.plsref_residuals(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), i64(comp), P(E))
         return E
 
     def sse(self, Xn, Yn, comp):
         Xn, Yn = F(Xn), F(Yn)
         out = np.zeros(self.M)
-        lib().plsref_sse(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), i64(comp), P(out))
+        self._lib.plsref_sse(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), i64(comp), P(out))
         return out
 
     def explained_variance(self, Xn, Yn, comp):
         Xn, Yn = F(Xn), F(Yn)
         out = np.zeros(self.M)
-        lib().plsref_explained_variance(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), i64(comp),
+        self._lib.plsref_explained_variance(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), i64(comp),
                                         P(out))
         return out
 
     def cv_loo(self):
         """The reference's own cv_LOO (inner models extract K components: slow)."""
         E = np.zeros((self.M, self.A, self.N))
-        lib().plsref_cv_loo(self.h, P(E))
+        self._lib.plsref_cv_loo(self.h, P(E))
         return E.transpose(0, 2, 1)
 
     def cv_lso(self, frac, trials, seed=5489):
         test_size = int(frac * self.N + 0.5)
         E = np.zeros((self.M, self.A, trials * test_size))
-        lib().plsref_cv_lso(self.h, C.c_double(frac), i64(trials), C.c_uint32(seed), P(E))
+        self._lib.plsref_cv_lso(self.h, C.c_double(frac), i64(trials), C.c_uint32(seed), P(E))
         return E.transpose(0, 2, 1)
 
     def cv_new_data(self, Xn, Yn):
         Xn, Yn = F(Xn), F(Yn)
         E = np.zeros((self.M, self.A, Xn.shape[0]))
-        lib().plsref_cv_new_data(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), P(E))
+        self._lib.plsref_cv_new_data(self.h, P(Xn), i64(Xn.shape[0]), i64(self.K), P(Yn), i64(self.M), P(E))
         return E.transpose(0, 2, 1)
 
 
@@ -221,15 +225,36 @@ _SO_OMP = os.path.join(_HERE, "_ref", "libplsref_omp.so")
 _lib_omp = None
 
 
-def time_fit_omp(X, Y, A, method=0, reps=1):
-    """time_fit on the -fopenmp build of the same reference sources (Eigen threads its GEMM kernels only);
-    None when that build is absent."""
+def _bind(l):
+    l.plsref_model_new.restype = C.c_void_p
+    l.plsref_model_max_imag.restype = C.c_double
+    l.plsref_wilcoxon.restype = C.c_double
+    l.plsref_normalcdf.restype = C.c_double
+    l.plsref_normalcdf.argtypes = [C.c_double]
+    l.plsref_time_fit.restype = C.c_double
+    l.plsref_read_matrix_file.restype = C.c_int64
+    return l
+
+
+def lib_omp():
+    """The -fopenmp build (None-safe callers check omp_available())."""
     global _lib_omp
     if _lib_omp is None:
         if not os.path.exists(_SO_OMP):
-            return None
-        _lib_omp = C.CDLL(_SO_OMP)
-        _lib_omp.plsref_time_fit.restype = C.c_double
+            raise RuntimeError("oracle/_ref/libplsref_omp.so not built")
+        _lib_omp = _bind(C.CDLL(_SO_OMP))
+    return _lib_omp
+
+
+def omp_available():
+    return os.path.exists(_SO_OMP)
+
+
+def time_fit_omp(X, Y, A, method=0, reps=1):
+    """time_fit on the -fopenmp build of the same reference sources (Eigen threads its GEMM kernels only);
+    None when that build is absent."""
+    if not omp_available():
+        return None
     X, Y = F(X), F(Y)
-    return _lib_omp.plsref_time_fit(P(X), i64(X.shape[0]), i64(X.shape[1]), P(Y), i64(Y.shape[1]), C.c_int(method),
+    return lib_omp().plsref_time_fit(P(X), i64(X.shape[0]), i64(X.shape[1]), P(Y), i64(Y.shape[1]), C.c_int(method),
                                     i64(A), C.c_int(reps))

@@ -22,9 +22,9 @@ SYMBOLS = [
     "plsb_comm_unique_id", "plsb_comm_init", "plsb_comm_allreduce_test",
     "plsb_dataset_create", "plsb_dataset_create_device", "plsb_dataset_create_synth", "plsb_dataset_destroy",
     "plsb_dataset_shape", "plsb_dataset_download", "plsb_dataset_set_sharded",
-    "plsb_fit", "plsb_fit_host", "plsb_xty", "plsb_xtx",
+    "plsb_fit", "plsb_fit_resident", "plsb_model_download", "plsb_model_destroy", "plsb_fit_host", "plsb_xty", "plsb_xtx",
     "plsb_scores", "plsb_fitted", "plsb_predict_residuals", "plsb_coefficients", "plsb_sse_prefixes", "plsb_sse",
-    "plsb_cv_folds", "plsb_colstats", "plsb_colwise_z_scores", "plsb_dataset_zscore",
+    "plsb_cv_folds", "plsb_cv_folds_press", "plsb_colstats", "plsb_colwise_z_scores", "plsb_dataset_zscore",
     "plsb_normalcdf", "plsb_wilcoxon", "plsb_validation", "plsb_optimal_num_components", "plsb_lso_folds",
     "plsb_profile_enable", "plsb_profile_reset", "plsb_profile_get", "plsb_launch_count",
 ]
@@ -177,8 +177,28 @@ class Dataset:
         return dict(W=W, P=Pm, R=R, Q=Q, T=T)
 
     def fit_nocopy(self, A, method=0):
-        """fit without reading results back (device-resident throughput runs)"""
+        """fit without reading results back and WITHOUT forming the scores T (A/B only: the reference's KERNEL_TYPE1
+        fit stores T, so throughput figures use fit_resident)"""
         check(lib().plsb_fit(self.h, i64(A), C.c_int(method), None, None, None, None, None))
+
+    def fit_resident(self, A, method=0, download=None):
+        """the complete fit (W, P, R, Q and, KERNEL_TYPE1, the N x A scores T) formed and kept in HBM;
+        download: None, or a string of matrix names ("WPRQ", "T", ...) to read back before the model is released"""
+        mh = C.c_void_p()
+        check(lib().plsb_fit_resident(self.h, i64(A), C.c_int(method), C.byref(mh)))
+        out = None
+        try:
+            if download:
+                K, M, N = self.K, self.M, self.N
+                out = {k: np.zeros((K, A), order="F") for k in "WPR" if k in download}
+                if "Q" in download:
+                    out["Q"] = np.zeros((M, A), order="F")
+                if "T" in download:
+                    out["T"] = np.zeros((N, A), order="F")
+                check(lib().plsb_model_download(mh, *[P(out.get(k)) for k in "WPRQT"]))
+        finally:
+            lib().plsb_model_destroy(mh)
+        return out
 
     def xty(self):
         S = np.zeros((self.K, self.M), order="F")
@@ -201,6 +221,17 @@ class Dataset:
         check(lib().plsb_cv_folds(self.h, i64(A), C.c_int(method), i64(ntot), i64(ts), IP(test_idx), i64(fold0),
                                   i64(nloc), P(out)))
         return out.transpose(0, 2, 1)
+
+    def cv_press(self, A, method, test_idx, fold0=0, nfolds_local=None, want_E=False):
+        """PRESS sums (M x A) of this call's folds reduced on the device; the residual block stays there unless want_E."""
+        test_idx = np.ascontiguousarray(test_idx, dtype=np.int64)
+        ntot, ts = test_idx.shape
+        nloc = ntot - fold0 if nfolds_local is None else nfolds_local
+        press = np.zeros((self.M, A), order="F")
+        E = np.zeros((self.M, A, ntot * ts)) if want_E else None
+        check(lib().plsb_cv_folds_press(self.h, i64(A), C.c_int(method), i64(ntot), i64(ts), IP(test_idx), i64(fold0),
+                                        i64(nloc), P(E), P(press)))
+        return (press, E.transpose(0, 2, 1)) if want_E else press
 
 
 def colstats(ctx, X, means=None):

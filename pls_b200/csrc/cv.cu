@@ -315,45 +315,129 @@ struct CvBuf {
     double *d() { return (double *)p; }
 };
 
+// PRESS partial sums on the device (validation's column sums of squared residuals, reference src/pls.cpp:248-252):
+// press[mc] = sum over this call's rows of E[mc][row]^2, two fixed-shape stages (1024-row blocks summed by one CTA
+// each, block totals added in block order): deterministic, no atomics.
+__global__ void __launch_bounds__(256) press_blocks_kernel(const double *__restrict__ E, int64_t rows, int nblk,
+                                                           double *__restrict__ part) {
+    __shared__ double red[8];
+    const int mc = blockIdx.y, b = blockIdx.x;
+    const double *col = E + (size_t)mc * rows;
+    const int64_t r0 = (int64_t)b * 1024;
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int64_t i = r0 + threadIdx.x + 256 * j;
+        if (i < rows) { const double e = col[i]; acc = fma(e, e, acc); }
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tsum = 0.0;
+#pragma unroll
+        for (int wv = 0; wv < 8; ++wv) tsum += red[wv];
+        part[(size_t)mc * nblk + b] = tsum;
+    }
+}
+__global__ void __launch_bounds__(256) press_final_kernel(const double *__restrict__ part, int nblk, double *__restrict__ out) {
+    __shared__ double red[256];
+    const double *p = part + (size_t)blockIdx.x * nblk;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < nblk; i += 256) acc += p[i];     // thread t: blocks t, t+256, ... in order
+    red[threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double tsum = 0.0;
+        for (int i = 0; i < 256; ++i) tsum += red[i];
+        out[blockIdx.x] = tsum;
+    }
+}
+
+static int device_press(plsb_ctx *c, const double *Ed, int64_t rows, int64_t MA, double *press_host) {
+    const int nblk = (int)ceil_div(rows, 1024);
+    CvBuf part(c), out(c);
+    PLSB_TRY(part.alloc((size_t)MA * nblk * 8));
+    PLSB_TRY(out.alloc((size_t)MA * 8));
+    press_blocks_kernel<<<dim3((unsigned)nblk, (unsigned)MA), 256, 0, c->stream>>>(Ed, rows, nblk, part.d());
+    press_final_kernel<<<(unsigned)MA, 256, 0, c->stream>>>(part.d(), nblk, out.d());
+    c->launches += 2;
+    PLSB_CUDA(cudaGetLastError());
+    PLSB_CUDA(cudaMemcpyAsync(press_host, out.p, (size_t)MA * 8, cudaMemcpyDeviceToHost, c->stream));
+    return PLSB_OK;
+}
+
+// small-data regime (cv_small.cu)
+bool cv_small_supported(const plsb_ctx *c, const plsb_dataset *ds, int64_t A, int64_t ts, bool *pr_in_smem);
+int launch_cv_small(plsb_ctx *c, const plsb_dataset *ds, int64_t A, const int64_t *idx_dev, int64_t nf, int64_t ts,
+                    int64_t rows_local, double *Ed, bool pr_in_smem);
+
 }  // namespace plsb
 
 using namespace plsb;
 
-extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
-                             const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E) {
-    PLSB_ARG(ds && test_idx && E, "null argument");
+extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
+                                   const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E, double *press) {
+    PLSB_ARG(ds && test_idx && (E || press), "null argument");
     PLSB_ARG(A >= 1, "A must be >= 1");
     PLSB_ARG(method == PLSB_KERNEL_TYPE1 || method == PLSB_KERNEL_TYPE2, "unknown method %d", method);
     PLSB_ARG(test_size >= 1 && test_size < ds->N, "test_size %lld must be in [1, N)", (long long)test_size);
     PLSB_ARG(fold0 >= 0 && nfolds_local >= 0 && fold0 + nfolds_local <= nfolds_total, "bad fold range");
-    PLSB_ARG(ds->M <= PLSB_MAX_M, "M=%lld exceeds the in-kernel eigen solver limit (%d)", (long long)ds->M, PLSB_MAX_M);
+    if (ds->M > PLSB_MAX_M) {
+        set_error("M=%lld responses exceed the in-kernel eigen solver limit (%d)", (long long)ds->M, PLSB_MAX_M);
+        return PLSB_ERR_UNSUPPORTED;
+    }
     PLSB_ARG(!ds->sharded, "cross-validation wants the full data set on every GPU (folds are sharded, not rows)");
-    if (nfolds_local == 0) return PLSB_OK;
+    const int64_t K = ds->K, ldk = ds->ldk, M = ds->M, ts = test_size;
+    if (nfolds_local == 0) {
+        if (press) for (int64_t i = 0; i < M * A; ++i) press[i] = 0.0;
+        return PLSB_OK;
+    }
     plsb_ctx *c = ds->ctx;
     PLSB_CUDA(cudaSetDevice(c->device));
-    const int64_t K = ds->K, ldk = ds->ldk, M = ds->M, ts = test_size;
     const int64_t *tloc = test_idx + fold0 * ts;
     for (int64_t i = 0; i < nfolds_local * ts; ++i)
         PLSB_ARG(tloc[i] >= 0 && tloc[i] < ds->N, "test index %lld out of range", (long long)tloc[i]);
     const int64_t rows_local = nfolds_local * ts, rows_total = nfolds_total * ts;
 
     CvBuf G(c), S0(c), idx(c), Ed(c), S(c), P(c), R(c), w(c), Gr(c), U(c);
+    PLSB_TRY(idx.alloc((size_t)rows_local * sizeof(int64_t)));
+    PLSB_CUDA(cudaMemcpyAsync(idx.p, tloc, (size_t)rows_local * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+    PLSB_TRY(Ed.alloc((size_t)M * A * rows_local * 8));
+
+    auto finish = [&]() -> int {
+        if (press) PLSB_TRY(device_press(c, Ed.d(), rows_local, M * A, press));
+        if (E) PLSB_CUDA(cudaMemcpy2DAsync(E + fold0 * ts, (size_t)rows_total * 8, Ed.p, (size_t)rows_local * 8,
+                                           (size_t)rows_local * 8, (size_t)(M * A), cudaMemcpyDeviceToHost, c->stream));
+        PLSB_CUDA(cudaStreamSynchronize(c->stream));
+        return PLSB_OK;
+    };
+
+    // small-data regime: the whole data set in one SM's shared memory, one launch for the call (cv_small.cu)
+    {
+        bool pr_in_smem = false;
+        const char *off = getenv("PLSB_CV_NO_SMALL");
+        if (!(off && *off == '1') && cv_small_supported(c, ds, A, ts, &pr_in_smem)) {
+            PLSB_TRY(launch_cv_small(c, ds, A, (const int64_t *)idx.p, nfolds_local, ts, rows_local, Ed.d(), pr_in_smem));
+            return finish();
+        }
+    }
+
     const int64_t ldg = round_up(K, 2);
     PLSB_TRY(G.alloc((size_t)K * ldg * 8));
     PLSB_CUDA(cudaMemsetAsync(G.p, 0, (size_t)K * ldg * 8, c->stream));
     PLSB_TRY(S0.alloc((size_t)M * ldk * 8));
     PLSB_TRY(launch_xtx(c, ds, G.d(), ldg));
     PLSB_TRY(launch_xty_pass(c, ds, S0.d()));
-    PLSB_TRY(idx.alloc((size_t)rows_local * sizeof(int64_t)));
-    PLSB_CUDA(cudaMemcpyAsync(idx.p, tloc, (size_t)rows_local * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
-    PLSB_TRY(Ed.alloc((size_t)M * A * rows_local * 8));
 
-    // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles
+    // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles.  At most 4736
+    // folds = 37 column tiles of the batched GEMM: with K = 4096 (32 row tiles) that is 1184 CTAs = 8 full waves of
+    // 148 SMs, with K = 2048 four.
     size_t free_b = 0;
     PLSB_TRY(dev_mem_available(c, &free_b));
     const size_t per_fold = (size_t)(M + 2 * A + 2) * ldk * 8 + (size_t)ts * 8;
     int64_t F = (int64_t)((double)free_b * 0.6 / (double)per_fold);
-    if (F > 4096) F = 4096;
+    if (F > 4736) F = 4736;
     if (const char *e = getenv("PLSB_FOLD_BATCH")) { const int64_t v = atoll(e); if (v > 0 && v < F) F = v; }
     if (F > nfolds_local) F = nfolds_local;
     PLSB_ARG(F >= 1, "not enough device memory for one fold");
@@ -394,8 +478,11 @@ extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t n
             PLSB_CUDA(cudaGetLastError());
         }
     }
-    PLSB_CUDA(cudaMemcpy2DAsync(E + fold0 * ts, (size_t)rows_total * 8, Ed.p, (size_t)rows_local * 8,
-                                (size_t)rows_local * 8, (size_t)(M * A), cudaMemcpyDeviceToHost, c->stream));
-    PLSB_CUDA(cudaStreamSynchronize(c->stream));
-    return PLSB_OK;
+    return finish();
+}
+
+extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
+                             const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E) {
+    PLSB_ARG(E, "null argument");
+    return plsb_cv_folds_press(ds, A, method, nfolds_total, test_size, test_idx, fold0, nfolds_local, E, nullptr);
 }

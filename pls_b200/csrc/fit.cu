@@ -153,6 +153,64 @@ int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, dou
     return PLSB_OK;
 }
 
+// ---- resident models: the fit's results (W, P, R, Q and the scores T) are formed in HBM and stay there --------------
+int plsb_fit_resident(plsb_dataset_t ds, int64_t A, int method, plsb_model_t *out) {
+    PLSB_ARG(ds && out, "null argument");
+    PLSB_ARG(A >= 1, "A must be >= 1");
+    PLSB_ARG(method == PLSB_KERNEL_TYPE1 || method == PLSB_KERNEL_TYPE2, "unknown method %d", method);
+    plsb_ctx *c = ds->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    plsb_model *m = new plsb_model();
+    m->ctx = c; m->N = ds->N; m->K = ds->K; m->ldk = ds->ldk; m->M = ds->M; m->A = A; m->method = method;
+    const bool wantT = method == PLSB_KERNEL_TYPE1 && ds->N > 0;   // the reference stores T for KERNEL_TYPE1 only (pls.cpp:394, 434)
+    int rc = dev_alloc(c, (void **)&m->W, (size_t)A * m->ldk * 8);
+    if (rc == PLSB_OK) rc = dev_alloc(c, (void **)&m->P, (size_t)A * m->ldk * 8);
+    if (rc == PLSB_OK) rc = dev_alloc(c, (void **)&m->R, (size_t)A * m->ldk * 8);
+    if (rc == PLSB_OK) rc = dev_alloc(c, (void **)&m->Q, (size_t)A * m->M * 8);
+    if (rc == PLSB_OK && wantT) rc = dev_alloc(c, (void **)&m->T, (size_t)A * m->N * 8);
+    if (rc == PLSB_OK) {
+        cudaError_t e = cudaMemsetAsync(m->W, 0, (size_t)A * m->ldk * 8, c->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(m->P, 0, (size_t)A * m->ldk * 8, c->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(m->R, 0, (size_t)A * m->ldk * 8, c->stream);
+        if (e == cudaSuccess) e = cudaMemsetAsync(m->Q, 0, (size_t)A * m->M * 8, c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "cudaMemsetAsync", __FILE__, __LINE__);
+    }
+    if (rc == PLSB_OK) rc = fit_device(ds, A, method, m->W, m->P, m->R, m->Q, m->T);
+    if (rc == PLSB_OK) {
+        cudaError_t e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "fit", __FILE__, __LINE__);
+    }
+    if (rc == PLSB_OK && ds->sharded) rc = xchg_check(c);
+    if (rc != PLSB_OK) { plsb_model_destroy(m); return rc; }
+    *out = m;
+    return PLSB_OK;
+}
+
+int plsb_model_download(plsb_model_t m, double *W, double *P, double *R, double *Q, double *T) {
+    PLSB_ARG(m, "model is null");
+    plsb_ctx *c = m->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    const size_t kb = (size_t)m->K * 8, lb = (size_t)m->ldk * 8, A = (size_t)m->A;
+    if (W) PLSB_CUDA(cudaMemcpy2DAsync(W, kb, m->W, lb, kb, A, cudaMemcpyDeviceToHost, c->stream));
+    if (P) PLSB_CUDA(cudaMemcpy2DAsync(P, kb, m->P, lb, kb, A, cudaMemcpyDeviceToHost, c->stream));
+    if (R) PLSB_CUDA(cudaMemcpy2DAsync(R, kb, m->R, lb, kb, A, cudaMemcpyDeviceToHost, c->stream));
+    if (Q) PLSB_CUDA(cudaMemcpyAsync(Q, m->Q, A * m->M * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (T) {
+        PLSB_ARG(m->T, "this model holds no scores (KERNEL_TYPE2 stores none, pls.cpp:394)");
+        PLSB_CUDA(cudaMemcpyAsync(T, m->T, A * m->N * 8, cudaMemcpyDeviceToHost, c->stream));
+    }
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
+}
+
+int plsb_model_destroy(plsb_model_t m) {
+    if (!m) return PLSB_OK;
+    cudaSetDevice(m->ctx->device);
+    dev_free(m->ctx, m->W); dev_free(m->ctx, m->P); dev_free(m->ctx, m->R); dev_free(m->ctx, m->Q); dev_free(m->ctx, m->T);
+    delete m;
+    return PLSB_OK;
+}
+
 int plsb_fit_host(plsb_ctx_t c, const double *X, int64_t ldx, int64_t N, int64_t K, const double *Y, int64_t ldy,
                   int64_t M, int64_t A, int method, double *W, double *P, double *R, double *Q, double *T) {
     plsb_dataset_t ds = nullptr;

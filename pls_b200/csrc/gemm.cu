@@ -4,7 +4,16 @@
 // product XX * R_batch of the cross-validation engine.  Operands are "k-major": A is Kd x M and B is
 // Kd x N, both row-major (the reduction index is the slow one), which is exactly how X (rows = samples)
 // and the fold-minor vector batches sit in HBM.  FP64 has no tcgen05 kind on sm_100a: the tensor path
-// is warp-level mma.sync m8n8k4 (SASS DMMA), fed from shared memory tiles staged with cp.async.
+// is warp-level mma.sync m8n8k4 (SASS DMMA.8x8x4; the wider PTX shapes m16n8k4/k8/k16 decompose into the
+// same instruction on sm_100a).
+//
+// dmma_tma_kernel (default): a warp-specialised pipeline.  One PRODUCER warp keeps a ring of shared-memory
+// stages filled with 1-D TMA bulk copies (cp.async.bulk + mbarrier complete_tx, SASS UBLKCP) — one copy per
+// k-row of a k-major tile, one per column of an n-major B tile, each landing at a PADDED stride so that the
+// fragment loads are bank-conflict free — and the CONSUMER warps do nothing but LDS + DMMA between a `full`
+// wait and an `empty` arrive: no CTA-wide barrier and no address arithmetic in the k-loop.  (The first
+// version, dmma_atb_kernel below, staged with cp.async from all warps behind a __syncthreads() per k-tile: the
+// ~25 integer instructions per 16-byte copy drained the tensor pipe after every barrier — 81 % pipe-active, ncu.)
 //
 // Split-K over the reduction axis fills the 148 SMs; partial tiles go to scratch and are summed in
 // split order by a second kernel (no atomics: deterministic).  SYRK mode computes only tiles on or
@@ -167,6 +176,155 @@ __global__ void __launch_bounds__(GM_NT, 1) dmma_atb_kernel(const GemmArgs g) {
         }
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Warp-specialised TMA pipeline (see the header).  CW consumer warps in a (CW/4) x 4 grid over the 128 x 128 tile
+// (CW = 8: 64 x 32 per warp), + 1 producer warp.  Stage = A tile [BK][GT_LD] + B tile ([BK][GT_LD] k-major or
+// [BN][GT_LDBN] n-major), 3 stages of depth 32.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int GT_BK = 32, GT_LD = 132, GT_LDBN = GT_BK + 4, GT_STAGES = 3;
+constexpr int GT_A_BYTES = GT_BK * GT_LD * 8;
+__host__ __device__ constexpr int gt_b_bytes(bool nm) { return nm ? GM_BN * GT_LDBN * 8 : GT_BK * GT_LD * 8; }
+__host__ __device__ constexpr int gt_stage_bytes(bool nm) { return GT_A_BYTES + gt_b_bytes(nm); }
+
+__device__ __forceinline__ void gt_mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <bool B_NMAJOR, int CW>
+__global__ void __launch_bounds__((CW + 1) * 32) __maxnreg__(CW == 8 ? 224 : 120) dmma_tma_kernel(const GemmArgs g) {
+    extern __shared__ __align__(128) char smem[];
+    constexpr int STAGE = gt_stage_bytes(B_NMAJOR);
+    constexpr int WM = GM_BM / (CW / 4), MI = WM / 8;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)GT_STAGES * STAGE);
+    uint64_t *empty = full + GT_STAGES;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x % g.ntiles, split = blockIdx.x / g.ntiles;
+    int tm, tn;
+    if (g.syrk) syrk_tile(tile, g.tiles_m, tm, tn);
+    else { tm = tile / g.tiles_n; tn = tile % g.tiles_n; }
+    const int m_base = tm * GM_BM, n_base = tn * GM_BN;
+    const int64_t k_begin = (int64_t)split * g.k_per_split;
+    int64_t k_end = k_begin + g.k_per_split;
+    if (k_end > g.Kd) k_end = g.Kd;
+    const int nk = k_begin < k_end ? (int)((k_end - k_begin + GT_BK - 1) / GT_BK) : 0;
+    if (tid == 0) {
+        for (int s = 0; s < GT_STAGES; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], CW);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    if (warp == CW) {
+        // ---- producer: bulk copies of the valid part of each tile row; rows / columns past the matrix edge are
+        // never copied (the consumers mask the k tail, and out-of-range output rows / columns are discarded) ----
+        int a_cols = g.M - m_base; a_cols = a_cols > GM_BM ? GM_BM : (a_cols + 1) & ~1;
+        int b_cols = g.N - n_base; b_cols = b_cols > GM_BN ? GM_BN : b_cols;          // n-major: rows of the B tile
+        const int b_cols2 = (b_cols + 1) & ~1;                                       // k-major: doubles per k-row
+        for (int kt = 0; kt < nk; ++kt) {
+            const int s = kt % GT_STAGES;
+            if (kt >= GT_STAGES) mbar_wait(&empty[s], (uint32_t)(((kt / GT_STAGES) - 1) & 1));
+            const int64_t k0 = k_begin + (int64_t)kt * GT_BK;
+            const int kv = (int)(k_end - k0 < GT_BK ? k_end - k0 : GT_BK);
+            const int kv2 = (kv + 1) & ~1;
+            char *sa = smem + (size_t)s * STAGE, *sb = sa + GT_A_BYTES;
+            const uint32_t bytes = (uint32_t)kv * (uint32_t)a_cols * 8u +
+                                   (B_NMAJOR ? (uint32_t)b_cols * (uint32_t)kv2 * 8u : (uint32_t)kv * (uint32_t)b_cols2 * 8u);
+            if (lane == 0) mbar_arrive_expect_tx(&full[s], bytes);
+            __syncwarp();
+            if (lane < kv) {
+                bulk_g2s(sa + (size_t)lane * GT_LD * 8, g.A + (k0 + lane) * g.lda + m_base, (uint32_t)a_cols * 8u, &full[s]);
+                if (!B_NMAJOR)
+                    bulk_g2s(sb + (size_t)lane * GT_LD * 8, g.B + (k0 + lane) * g.ldb + n_base, (uint32_t)b_cols2 * 8u, &full[s]);
+            }
+            if (B_NMAJOR) {
+#pragma unroll
+                for (int i = 0; i < GM_BN / 32; ++i) {
+                    const int n = lane + 32 * i;
+                    if (n < b_cols)
+                        bulk_g2s(sb + (size_t)n * GT_LDBN * 8, g.B + (int64_t)(n_base + n) * g.ldb + k0, (uint32_t)kv2 * 8u, &full[s]);
+                }
+            }
+        }
+        return;
+    }
+
+    // ---- consumers ------------------------------------------------------------------------------------------------
+    double acc[MI][4][2];
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+    const int wm = (warp >> 2) * WM, wn = (warp & 3) * 32;
+    const int fk = lane & 3, fr = lane >> 2;
+    for (int kt = 0; kt < nk; ++kt) {
+        const int s = kt % GT_STAGES;
+        mbar_wait(&full[s], (uint32_t)((kt / GT_STAGES) & 1));
+        const double *as = reinterpret_cast<const double *>(smem + (size_t)s * STAGE) + fk * GT_LD + wm + fr;
+        const double *bs = reinterpret_cast<const double *>(smem + (size_t)s * STAGE + GT_A_BYTES) +
+                           (B_NMAJOR ? (wn + fr) * GT_LDBN + fk : fk * GT_LD + wn + fr);
+        const int64_t kleft = k_end - (k_begin + (int64_t)kt * GT_BK);
+        if (kleft >= GT_BK) {
+#pragma unroll
+            for (int kk = 0; kk < GT_BK / 4; ++kk) {
+                double a[MI], b[4];
+#pragma unroll
+                for (int i = 0; i < MI; ++i) a[i] = as[kk * 4 * GT_LD + i * 8];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) b[j] = B_NMAJOR ? bs[j * 8 * GT_LDBN + kk * 4] : bs[kk * 4 * GT_LD + j * 8];
+#pragma unroll
+                for (int i = 0; i < MI; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            }
+        } else {   // last k-tile of a split: rows past the end were not copied and hold stale shared memory
+            const int kv = (int)kleft;
+#pragma unroll 1
+            for (int kk = 0; kk * 4 < kv; ++kk) {
+                const bool live = kk * 4 + fk < kv;
+                double a[MI], b[4];
+#pragma unroll
+                for (int i = 0; i < MI; ++i) a[i] = live ? as[kk * 4 * GT_LD + i * 8] : 0.0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    b[j] = live ? (B_NMAJOR ? bs[j * 8 * GT_LDBN + kk * 4] : bs[kk * 4 * GT_LD + j * 8]) : 0.0;
+#pragma unroll
+                for (int i = 0; i < MI; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) gt_mbar_arrive(&empty[s]);
+    }
+    if (g.splitk == 1 && !g.syrk && !g.accum) {  // no partials needed: write the product directly
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int m = m_base + wm + i * 8 + fr, n = n_base + wn + j * 8 + fk * 2;
+                if (m >= g.M) continue;
+                if (!g.transC) {
+                    if (n < g.N) g.C[(int64_t)m * g.ldc + n] = acc[i][j][0];
+                    if (n + 1 < g.N) g.C[(int64_t)m * g.ldc + n + 1] = acc[i][j][1];
+                } else {
+                    if (n < g.N) g.C[(int64_t)n * g.ldc + m] = acc[i][j][0];
+                    if (n + 1 < g.N) g.C[(int64_t)(n + 1) * g.ldc + m] = acc[i][j][1];
+                }
+            }
+        return;
+    }
+    double *out = g.part + ((size_t)split * g.ntiles + tile) * (GM_BM * GM_BN);
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int row = wm + i * 8 + fr, col = wn + j * 8 + fk * 2;
+            *reinterpret_cast<double2 *>(out + row * GM_BN + col) = make_double2(acc[i][j][0], acc[i][j][1]);
+        }
+}
+
 // C[m*ldc + n] = sum_s part[s][tile][...]; SYRK also writes the mirrored element
 __global__ void __launch_bounds__(256) gemm_reduce_kernel(const GemmArgs g, double *__restrict__ C, int64_t ldc) {
     const int tile = blockIdx.x;
@@ -198,11 +356,19 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
     g.tiles_m = (int)ceil_div(M, GM_BM);
     g.tiles_n = (int)ceil_div(N, GM_BN);
     g.ntiles = syrk ? g.tiles_m * (g.tiles_m + 1) / 2 : g.tiles_m * g.tiles_n;
-    // enough CTAs for ~4 waves, but at least 64 k-steps per split
-    int64_t want = ceil_div((int64_t)4 * c->sm_count, g.ntiles);
+    // Split-K: at least 64 k-steps per split, at most ~12 waves of CTAs, and among those the smallest split count
+    // whose last wave is (nearly) full — one CTA per SM, so a grid of 4.3 waves costs 5 (C4 X'X: 136 SYRK tiles
+    // x 13 splits = 1768 CTAs = 11.95 waves instead of 5 splits = 4.59; a 2500-fold CV wave: 640 tiles x 2).
     int64_t maxsplit = ceil_div(Kd, (int64_t)GM_BK * 64);
-    if (want > maxsplit) want = maxsplit;
-    if (want < 1) want = 1;
+    if (maxsplit > 64) maxsplit = 64;
+    int64_t want = 1;
+    double best_eff = -1.0;
+    for (int64_t sp = 1; sp <= maxsplit; ++sp) {
+        const int64_t ctas = (int64_t)g.ntiles * sp;
+        if (sp > 1 && ctas > (int64_t)12 * c->sm_count) break;
+        const double eff = (double)ctas / (double)(ceil_div(ctas, c->sm_count) * c->sm_count);
+        if (eff > best_eff + 0.02) { best_eff = eff; want = sp; }
+    }
     g.k_per_split = round_up(ceil_div(Kd > 0 ? Kd : 1, want), GM_BK);
     g.splitk = (int)ceil_div(Kd > 0 ? Kd : 1, g.k_per_split);
     const bool direct = g.splitk == 1 && !syrk && !accumulate;
@@ -211,12 +377,26 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
         PLSB_TRY(ensure_part(c, pbytes));
         g.part = c->part;
     }
-    const size_t smem = (size_t)GM_STAGES * (GM_BK * GM_LD + (b_nmajor ? GM_BS_NMAJOR : GM_BS_KMAJOR)) * sizeof(double);
-    auto kern = b_nmajor ? dmma_atb_kernel<true> : dmma_atb_kernel<false>;
-    PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    {
+    static const int variant = [] {   // A/B switches: PLSB_GEMM_V1=1 the cp.async kernel, PLSB_GEMM_CW=16 sixteen 32x32 consumer warps
+        const char *v1 = getenv("PLSB_GEMM_V1"), *cw = getenv("PLSB_GEMM_CW");
+        if (v1 && *v1 == '1') return 1;
+        return (cw && atoi(cw) == 16) ? 16 : 8;
+    }();
+    if (b_nmajor) PLSB_ARG(ldb >= round_up(Kd, 2), "gemm: an n-major B needs ldb >= Kd rounded up to even");
+    if (variant == 1) {
+        const size_t smem = (size_t)GM_STAGES * (GM_BK * GM_LD + (b_nmajor ? GM_BS_NMAJOR : GM_BS_KMAJOR)) * sizeof(double);
+        auto kern = b_nmajor ? dmma_atb_kernel<true> : dmma_atb_kernel<false>;
+        PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ProfScope ps(c, prof_slot);
         kern<<<(unsigned)(g.ntiles * g.splitk), GM_NT, smem, c->stream>>>(g);
+    } else {
+        const size_t smem = (size_t)GT_STAGES * gt_stage_bytes(b_nmajor) + 2 * GT_STAGES * sizeof(uint64_t) + 16;
+        void (*kern)(const GemmArgs) =
+            variant == 16 ? (b_nmajor ? dmma_tma_kernel<true, 16> : dmma_tma_kernel<false, 16>)
+                          : (b_nmajor ? dmma_tma_kernel<true, 8> : dmma_tma_kernel<false, 8>);
+        PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ProfScope ps(c, prof_slot);
+        kern<<<(unsigned)(g.ntiles * g.splitk), (variant + 1) * 32, smem, c->stream>>>(g);
     }
     PLSB_CUDA(cudaGetLastError());
     c->launches += 1;

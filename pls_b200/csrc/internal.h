@@ -57,6 +57,16 @@ struct plsb_dataset {
     int gram_agreed = -1;       // row-sharded: do ALL ranks hold a Gram matrix? (-1: not asked yet)
 };
 
+// a fitted model whose matrices live in HBM (plsb_fit_resident): component-major, like the fit driver's buffers
+struct plsb_model {
+    plsb_ctx *ctx = nullptr;
+    int64_t N = 0, K = 0, ldk = 0, M = 0, A = 0;
+    int method = 0;
+    double *W = nullptr, *P = nullptr, *R = nullptr;   // A x ldk
+    double *Q = nullptr;                               // A x M
+    double *T = nullptr;                               // A x N (KERNEL_TYPE1 only)
+};
+
 namespace plsb {
 
 int ensure_part(plsb_ctx *c, size_t bytes);

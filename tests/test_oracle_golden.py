@@ -111,3 +111,40 @@ def test_synth_properties():
     assert np.array_equal(X[500:600], Xb) and np.array_equal(Y[500:600], Yb)   # row blocks are consistent
     u = np.array([port.lib().orc_synth_u(9, i) for i in range(20000)])
     assert abs(u.mean()) < 0.02 and abs(u.var() - 0.25) < 0.01
+
+
+def test_extended_precision_fit_is_pinned_by_the_reference_goldens():
+    """oracle/pls_oracle_ext.c (the long-double yardstick used where two correct FP64 fits differ by more than 1e-9) must
+    agree with the reference's own results where conditioning is benign: the down-scaled synthetic configurations."""
+    from tests.util import state_err
+    for name in ("c4s", "c4s_odd", "c4s_m1"):
+        g = load_golden(name)
+        seed, N, K, M, A = (int(v) for v in g["meta"])
+        X, Y = port.synth(seed, N, K, M)
+        ext = port.fit_ext(X, Y, A)
+        e, by = state_err(ext, {k: g.get("t1_" + k) for k in "WPRQT"})
+        assert e <= 1e-10, (name, by)
+        assert relerr(port.coefficients(ext["R"], ext["Q"], A), g["t1_coef_A"]) <= 1e-11
+
+
+def test_full_size_fixtures_are_consistent():
+    """tests/golden/c4_full.npz / c5_full.npz (the reference at BASELINE.json's full sizes): shapes, the recorded
+    distances between independent evaluations, and coefficients == R Q' inside the fixture itself."""
+    import json
+    g = load_golden("c4_full")
+    seed, N, K, M, A = (int(v) for v in g["meta"])
+    assert (N, K, M, A) == (1_000_000, 2048, 8, 32) and g["W"].shape == (K, A) and g["T_sub"].shape == (192, A)
+    assert relerr(port.coefficients(g["R"], g["Q"], A), g["coef_A"]) <= 1e-13
+    assert relerr(port.coefficients(g["R"], g["Q"], 8), g["coef_8"]) <= 1e-13
+    d = json.loads(str(g["distances_json"]))
+    # the facts the GPU tests lean on: coefficients agree to ~3e-11 between every pair of evaluations, loadings only to
+    # 0.5-1.2e-9, and the reference's own result is as far from the exact fit as any of the others
+    for pair in ("oracle_type1_vs_reference_type1", "reference_type2_vs_reference_type1", "reference_type1_vs_extended"):
+        assert d[pair]["coefficients"] <= 1e-10 and 1e-10 <= d[pair]["P"] <= 2e-9, (pair, d[pair])
+    Xh, _ = port.synth(seed, 4, K, M)
+    assert np.array_equal(Xh[:, :8], g["x_head"])
+    g5 = load_golden("c5_full")
+    seed, N, K, M, A = (int(v) for v in g5["meta"])
+    assert (N, K, M, A) == (20_000, 4096, 4, 64) and g5["loo"].shape == (M, 8, A)
+    d5 = json.loads(str(g5["distances_json"]))
+    assert d5["oracle_loo_vs_reference"] <= 1e-9 and d5["reference_type1_vs_extended"]["P"] <= 1e-9
