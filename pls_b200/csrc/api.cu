@@ -150,6 +150,25 @@ static int prof_drain(plsb_ctx *c) {
     return PLSB_OK;
 }
 
+void ctx_retain(plsb_ctx *c) { c->refs.fetch_add(1, std::memory_order_relaxed); }
+
+void ctx_release(plsb_ctx *c) {
+    if (c->refs.fetch_sub(1, std::memory_order_acq_rel) != 1) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    xchg_teardown(c);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    for (auto e : c->pool) cudaEventDestroy(e);
+    if (c->part) cudaFreeAsync(c->part, c->stream);
+    cudaStreamSynchronize(c->stream);
+    cudaStreamDestroy(c->stream);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    for (int i = 0; i < 4; ++i) if (c->xfer_ev[i]) cudaEventDestroy(c->xfer_ev[i]);
+    if (c->col_ev) cudaEventDestroy(c->col_ev);
+    delete c;
+}
+
 }  // namespace plsb
 
 using namespace plsb;
@@ -197,20 +216,9 @@ int plsb_ctx_create(int device, plsb_ctx_t *out) {
 }
 
 int plsb_ctx_destroy(plsb_ctx_t c) {
-    if (!c) return PLSB_OK;
-    cudaSetDevice(c->device);
-    cudaStreamSynchronize(c->stream);
-    xchg_teardown(c);
-    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-    for (auto &p : c->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
-    for (auto e : c->pool) cudaEventDestroy(e);
-    if (c->part) cudaFreeAsync(c->part, c->stream);
-    cudaStreamSynchronize(c->stream);
-    cudaStreamDestroy(c->stream);
-    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
-    for (int i = 0; i < 4; ++i) if (c->xfer_ev[i]) cudaEventDestroy(c->xfer_ev[i]);
-    if (c->col_ev) cudaEventDestroy(c->col_ev);
-    delete c;
+    if (!c || c->closed) return PLSB_OK;
+    c->closed = true;
+    ctx_release(c);
     return PLSB_OK;
 }
 

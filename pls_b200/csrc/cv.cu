@@ -340,7 +340,9 @@ __global__ void __launch_bounds__(256) press_blocks_kernel(const double *__restr
         part[(size_t)mc * nblk + b] = tsum;
     }
 }
-__global__ void __launch_bounds__(256) press_final_kernel(const double *__restrict__ part, int nblk, double *__restrict__ out) {
+// out is validation's M x A matrix, column-major: out[c*M + m]  (block mc = m*A + c of the residual block)
+__global__ void __launch_bounds__(256) press_final_kernel(const double *__restrict__ part, int nblk, int M, int A,
+                                                          double *__restrict__ out) {
     __shared__ double red[256];
     const double *p = part + (size_t)blockIdx.x * nblk;
     double acc = 0.0;
@@ -350,17 +352,19 @@ __global__ void __launch_bounds__(256) press_final_kernel(const double *__restri
     if (threadIdx.x == 0) {
         double tsum = 0.0;
         for (int i = 0; i < 256; ++i) tsum += red[i];
-        out[blockIdx.x] = tsum;
+        const int m = blockIdx.x / A, cc = blockIdx.x % A;
+        out[(size_t)cc * M + m] = tsum;
     }
 }
 
-static int device_press(plsb_ctx *c, const double *Ed, int64_t rows, int64_t MA, double *press_host) {
+static int device_press(plsb_ctx *c, const double *Ed, int64_t rows, int64_t M, int64_t A, double *press_host) {
+    const int64_t MA = M * A;
     const int nblk = (int)ceil_div(rows, 1024);
     CvBuf part(c), out(c);
     PLSB_TRY(part.alloc((size_t)MA * nblk * 8));
     PLSB_TRY(out.alloc((size_t)MA * 8));
     press_blocks_kernel<<<dim3((unsigned)nblk, (unsigned)MA), 256, 0, c->stream>>>(Ed, rows, nblk, part.d());
-    press_final_kernel<<<(unsigned)MA, 256, 0, c->stream>>>(part.d(), nblk, out.d());
+    press_final_kernel<<<(unsigned)MA, 256, 0, c->stream>>>(part.d(), nblk, (int)M, (int)A, out.d());
     c->launches += 2;
     PLSB_CUDA(cudaGetLastError());
     PLSB_CUDA(cudaMemcpyAsync(press_host, out.p, (size_t)MA * 8, cudaMemcpyDeviceToHost, c->stream));
@@ -406,7 +410,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     PLSB_TRY(Ed.alloc((size_t)M * A * rows_local * 8));
 
     auto finish = [&]() -> int {
-        if (press) PLSB_TRY(device_press(c, Ed.d(), rows_local, M * A, press));
+        if (press) PLSB_TRY(device_press(c, Ed.d(), rows_local, M, A, press));
         if (E) PLSB_CUDA(cudaMemcpy2DAsync(E + fold0 * ts, (size_t)rows_total * 8, Ed.p, (size_t)rows_local * 8,
                                            (size_t)rows_local * 8, (size_t)(M * A), cudaMemcpyDeviceToHost, c->stream));
         PLSB_CUDA(cudaStreamSynchronize(c->stream));

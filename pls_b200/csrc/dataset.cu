@@ -109,9 +109,11 @@ static int upload_rows_with_gram(plsb_ctx *c, const double *src, int64_t lds, pl
 
 static int dataset_alloc(plsb_ctx *c, int64_t N, int64_t K, int64_t M, plsb_dataset **out) {
     PLSB_ARG(c && out, "null argument");
+    PLSB_ARG(!c->closed, "the context has been destroyed");
     PLSB_ARG(N >= 0 && K >= 1 && M >= 1, "bad shape N=%lld K=%lld M=%lld", (long long)N, (long long)K, (long long)M);
     PLSB_CUDA(cudaSetDevice(c->device));
     plsb_dataset *ds = new plsb_dataset();
+    ctx_retain(c);
     ds->ctx = c; ds->N = N; ds->K = K; ds->M = M;
     ds->ldk = round_up(K, 2);
     ds->ldm = round_up(M, 2);
@@ -124,7 +126,9 @@ static int dataset_alloc(plsb_ctx *c, int64_t N, int64_t K, int64_t M, plsb_data
         dev_free(c, ds->X);
         dev_free(c, ds->Y);
         delete ds;
-        return cuda_fail(e, "dataset alloc", __FILE__, __LINE__);
+        const int rc = cuda_fail(e, "dataset alloc", __FILE__, __LINE__);
+        ctx_release(c);
+        return rc;
     }
     *out = ds;
     return PLSB_OK;
@@ -185,7 +189,9 @@ int plsb_dataset_destroy(plsb_dataset_t ds) {
     dev_free(ds->ctx, ds->Y);
     dev_free(ds->ctx, ds->G);
     dev_free(ds->ctx, ds->S0);
+    plsb_ctx *c = ds->ctx;
     delete ds;
+    ctx_release(c);
     return PLSB_OK;
 }
 int plsb_dataset_shape(plsb_dataset_t ds, int64_t *N, int64_t *K, int64_t *M) {

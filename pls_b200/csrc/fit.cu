@@ -161,6 +161,7 @@ int plsb_fit_resident(plsb_dataset_t ds, int64_t A, int method, plsb_model_t *ou
     plsb_ctx *c = ds->ctx;
     PLSB_CUDA(cudaSetDevice(c->device));
     plsb_model *m = new plsb_model();
+    ctx_retain(c);
     m->ctx = c; m->N = ds->N; m->K = ds->K; m->ldk = ds->ldk; m->M = ds->M; m->A = A; m->method = method;
     const bool wantT = method == PLSB_KERNEL_TYPE1 && ds->N > 0;   // the reference stores T for KERNEL_TYPE1 only (pls.cpp:394, 434)
     int rc = dev_alloc(c, (void **)&m->W, (size_t)A * m->ldk * 8);
@@ -207,7 +208,9 @@ int plsb_model_destroy(plsb_model_t m) {
     if (!m) return PLSB_OK;
     cudaSetDevice(m->ctx->device);
     dev_free(m->ctx, m->W); dev_free(m->ctx, m->P); dev_free(m->ctx, m->R); dev_free(m->ctx, m->Q); dev_free(m->ctx, m->T);
+    plsb_ctx *c = m->ctx;
     delete m;
+    ctx_release(c);
     return PLSB_OK;
 }
 

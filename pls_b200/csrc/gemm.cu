@@ -191,7 +191,7 @@ __device__ __forceinline__ void gt_mbar_arrive(uint64_t *bar) {
 }
 
 template <bool B_NMAJOR, int CW>
-__global__ void __launch_bounds__((CW + 1) * 32) __maxnreg__(CW == 8 ? 224 : 120) dmma_tma_kernel(const GemmArgs g) {
+__global__ void __launch_bounds__((CW + 1) * 32) __maxnreg__(CW == 8 ? 168 : 96) dmma_tma_kernel(const GemmArgs g) {
     extern __shared__ __align__(128) char smem[];
     constexpr int STAGE = gt_stage_bytes(B_NMAJOR);
     constexpr int WM = GM_BM / (CW / 4), MI = WM / 8;

@@ -1,5 +1,6 @@
 // pls_b200/csrc/internal.h — private structures and kernel launchers of libplsb.so.
 #pragma once
+#include <atomic>
 #include <vector>
 
 #include "common.cuh"
@@ -8,6 +9,12 @@
 #define PLSB_XCHG_LEN 8192          /* doubles per exchange slot */
 
 struct plsb_ctx {
+    // Lifetime: the creator's handle is one reference, every data set / resident model holds another.  plsb_ctx_destroy
+    // drops the creator's; streams, communicator and scratch are torn down when the LAST reference goes, so a data set
+    // that outlives its context handle (a cached replica across PLS::set_devices, objects finalised in arbitrary order
+    // at interpreter exit) stays usable and destroyable.
+    std::atomic<int> refs{1};
+    bool closed = false;        // plsb_ctx_destroy was called: no new objects on this context
     int device = 0;
     int sm_count = 148;
     size_t smem_optin = 0;
@@ -69,6 +76,8 @@ struct plsb_model {
 
 namespace plsb {
 
+void ctx_retain(plsb_ctx *c);
+void ctx_release(plsb_ctx *c);   // tears the context down when the last reference goes
 int ensure_part(plsb_ctx *c, size_t bytes);
 // Stream-ordered allocations from the device's default memory pool.  plsb_ctx_create raises the pool's release
 // threshold so freed blocks stay cached: repeated fits / CV calls / uploads do not pay cudaMalloc again

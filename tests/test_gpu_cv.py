@@ -103,6 +103,19 @@ def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
         assert np.array_equal(ds.cv_folds(A, 0, te), got)
     finally:
         del os.environ["PLSB_FOLD_BATCH"]
+    # both regimes — one launch with the data set in shared memory (cv_small.cu, when it fits) and Gram downdates +
+    # batched DMMA GEMM (cv.cu) — against the same explicit refits
+    os.environ["PLSB_CV_NO_SMALL"] = "1"
+    try:
+        assert relerr(ds.cv_folds(A, 0, te), want) <= RTOL
+    finally:
+        del os.environ["PLSB_CV_NO_SMALL"]
+    # PRESS reduced on the device (validation's column sums, pls.cpp:248-252), residual block kept there
+    press = ds.cv_press(A, 0, te)
+    assert relerr(press, (got ** 2).sum(axis=1)) <= 1e-13
+    assert relerr(press, _capi.validation(got, 0)) <= 1e-13
+    p0 = ds.cv_press(A, 0, te, fold0=0, nfolds_local=h); p1 = ds.cv_press(A, 0, te, fold0=h, nfolds_local=nf - h)
+    assert relerr(p0 + p1, press) <= 1e-13
     ds.close()
 
 
