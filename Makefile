@@ -31,13 +31,15 @@ ifneq ($(EIGEN_INC),)
 # repo: EIGEN_INC points at a system Eigen or at the reference checkout's submodule.  On a box without
 # Eigen the prebuilt libpls.so / PLS / api_check (shipped with the snapshot) are used as they are.
 HOSTFLAGS := -std=c++17 -O2 -fPIC -Wall -Iinclude -I$(EIGEN_INC)
-host: pls_b200/libpls.so pls_b200/PLS tests/cpp/api_check
+host: pls_b200/libpls.so pls_b200/PLS tests/cpp/api_check tests/cpp/api_bench
 pls_b200/libpls.so: $(HOSTSRC) pls_b200/host/engine.h include/PLS/pls.h include/plsb.h $(LIB)
 	$(CXX) $(HOSTFLAGS) -shared -o $@ $(HOSTSRC) -Lpls_b200 -lplsb -lpthread -Wl,-rpath,'$$ORIGIN'
 pls_b200/PLS: pls_b200/host/main.cpp pls_b200/libpls.so
 	$(CXX) $(HOSTFLAGS) -o $@ pls_b200/host/main.cpp -Lpls_b200 -lpls -lplsb -lpthread -Wl,-rpath,'$$ORIGIN'
 tests/cpp/api_check: tests/cpp/api_check.cpp pls_b200/libpls.so
 	$(CXX) $(HOSTFLAGS) -o $@ tests/cpp/api_check.cpp -Lpls_b200 -lpls -lplsb -lpthread -Wl,-rpath,'$$ORIGIN/../../pls_b200'
+tests/cpp/api_bench: tests/cpp/api_bench.cpp pls_b200/libpls.so
+	$(CXX) $(HOSTFLAGS) -o $@ tests/cpp/api_bench.cpp -Lpls_b200 -lpls -lplsb -lpthread -Wl,-rpath,'$$ORIGIN/../../pls_b200'
 else
 host:
 	@echo "host: no Eigen headers found (set EIGEN_INC); using prebuilt libpls.so / PLS if present"
@@ -47,5 +49,5 @@ oracle:
 	$(MAKE) -C oracle
 
 clean:
-	rm -rf build $(LIB) pls_b200/libpls.so pls_b200/PLS tests/cpp/api_check
+	rm -rf build $(LIB) pls_b200/libpls.so pls_b200/PLS tests/cpp/api_check tests/cpp/api_bench
 .PHONY: all host oracle clean

@@ -168,12 +168,14 @@ struct Model {
     void print_state(std::ostream &os = std::cerr) const;
 
   private:
-    const Mat2D _X, _Y;  // the training data, kept for cv_LOO / cv_LSO
     size_t A;            // number of components
     Mat2Dc P, W, R, Q, T;
     PLS::METHOD method;
-    // device-resident copy of (_X, _Y), created by the constructor's fit and reused by cv_*
+    // The training data kept for cv_LOO / cv_LSO — the reference's `const Mat2D _X, _Y` (pls.h:251, copied at
+    // pls.cpp:344) — live in HBM only: the copy the constructor's fit uploads IS the model's copy (no second copy
+    // in host memory; later changes to the caller's matrices do not reach it, as in the reference).
     std::shared_ptr<detail::DeviceMirror> mirror;
+    void init_state(size_t num_predictors, size_t num_responses);
 
     Model(const size_t &num_predictors, const size_t &num_responses, const METHOD &algorithm = KERNEL_TYPE1);
     Model(const size_t &num_predictors, const size_t &num_responses, const METHOD &algorithm,

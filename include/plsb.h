@@ -55,6 +55,9 @@ int plsb_ctx_trim(plsb_ctx_t ctx);
 int plsb_comm_unique_id(void *id128);
 int plsb_comm_init(plsb_ctx_t ctx, int rank, int nranks, const void *id128);
 int plsb_comm_allreduce_test(plsb_ctx_t ctx, double *host_buf, int64_t n);
+/* What the context's communicator is: its rank / size, and whether the per-component [g | tt] exchange of a row-sharded
+ * fit runs inside the partial-sum kernel over NVLink peer memory (1) or as a separate ncclAllReduce (0). */
+int plsb_comm_info(plsb_ctx_t ctx, int *rank, int *nranks, int *peer_exchange);
 
 /* ---- datasets: Model's `_X,_Y` copy (pls.cpp:344) becomes a device-resident mirror ---------- */
 /* X: N x K, Y: N x M host column-major (pinned or pageable).  Rows are this rank's shard.
@@ -70,6 +73,13 @@ int plsb_dataset_create_device(plsb_ctx_t ctx, const double *dX, int64_t ldx, in
  * to oracle/pls_oracle.c:orc_synth.  Rows [row0, row0+N) of the global data set. */
 int plsb_dataset_create_synth(plsb_ctx_t ctx, uint64_t seed, int64_t row0, int64_t N, int64_t K,
                               int64_t M, int64_t L, plsb_dataset_t *ds);
+/* A new data set on ctx's device holding the rows of `parts` one after the other (device-to-device; parts on other
+ * GPUs are read over NVLink).  nparts = 1 replicates a data set onto another GPU, nparts = G gathers the row shards
+ * of a sharded fit into the full replica cross-validation wants — the training data are the Model's own copy
+ * (`_X,_Y`, pls.cpp:344, pls.h:251) and here that copy lives in HBM only, so replicas are made from it, not from
+ * the caller's host matrix.  Pageable host sources of plsb_dataset_create are packed into pinned staging buffers by
+ * a pool of host threads (PLSB_PACK_THREADS, default min(16, cores / contexts)) while earlier blocks are in flight. */
+int plsb_dataset_concat(plsb_ctx_t ctx, int64_t nparts, const plsb_dataset_t *parts, plsb_dataset_t *out);
 int plsb_dataset_destroy(plsb_dataset_t ds);
 int plsb_dataset_shape(plsb_dataset_t ds, int64_t *N, int64_t *K, int64_t *M);
 /* Copy the data set back to host column-major buffers (either may be NULL). */

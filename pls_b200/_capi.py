@@ -19,9 +19,9 @@ i64 = C.c_int64
 # symbols include/plsb.h declares (tests check that the library exports every one)
 SYMBOLS = [
     "plsb_last_error", "plsb_version", "plsb_device_count", "plsb_ctx_create", "plsb_ctx_destroy", "plsb_ctx_sync", "plsb_ctx_trim",
-    "plsb_comm_unique_id", "plsb_comm_init", "plsb_comm_allreduce_test",
+    "plsb_comm_unique_id", "plsb_comm_init", "plsb_comm_allreduce_test", "plsb_comm_info",
     "plsb_dataset_create", "plsb_dataset_create_device", "plsb_dataset_create_synth", "plsb_dataset_destroy",
-    "plsb_dataset_shape", "plsb_dataset_download", "plsb_dataset_set_sharded",
+    "plsb_dataset_shape", "plsb_dataset_concat", "plsb_dataset_download", "plsb_dataset_set_sharded",
     "plsb_fit", "plsb_fit_resident", "plsb_model_download", "plsb_model_destroy", "plsb_fit_host", "plsb_xty", "plsb_xtx",
     "plsb_scores", "plsb_fitted", "plsb_predict_residuals", "plsb_coefficients", "plsb_sse_prefixes", "plsb_sse",
     "plsb_cv_folds", "plsb_cv_folds_press", "plsb_colstats", "plsb_colwise_z_scores", "plsb_dataset_zscore",
@@ -102,6 +102,11 @@ class Context:
     def comm_init(self, rank, nranks, uid):
         check(lib().plsb_comm_init(self.h, C.c_int(rank), C.c_int(nranks), C.c_char_p(uid)))
 
+    def comm_info(self):
+        r, n, p = C.c_int(0), C.c_int(1), C.c_int(0)
+        check(lib().plsb_comm_info(self.h, C.byref(r), C.byref(n), C.byref(p)))
+        return {"rank": r.value, "nranks": n.value, "exchange": "peer" if p.value else ("nccl" if n.value > 1 else "none")}
+
     def allreduce_test(self, arr):
         arr = np.ascontiguousarray(arr, dtype=np.float64)
         check(lib().plsb_comm_allreduce_test(self.h, P(arr), i64(arr.size)))
@@ -149,6 +154,16 @@ class Dataset:
                                             i64(max(self.N, 1)), i64(self.M), C.byref(self.h)))
         if sharded:
             check(lib().plsb_dataset_set_sharded(self.h, C.c_int(1)))
+
+    @classmethod
+    def concat(cls, ctx, parts):
+        """the rows of `parts` (data sets on any GPUs) one after the other, as a new data set on ctx's device"""
+        self = cls.__new__(cls)
+        self.ctx, self.h = ctx, C.c_void_p()
+        arr = (C.c_void_p * len(parts))(*[p.h for p in parts])
+        check(lib().plsb_dataset_concat(ctx.h, i64(len(parts)), arr, C.byref(self.h)))
+        self.N, self.K, self.M = sum(p.N for p in parts), parts[0].K, parts[0].M
+        return self
 
     def close(self):
         if getattr(self, "h", None):

@@ -38,6 +38,7 @@ struct XchgArgs {
     char *area[PLSB_MAX_RANKS];   // every rank's exchange area (area[rank] is local)
     unsigned *counter;   // device-scope arrival counter (local)
     int *err;            // local error flag (timeout)
+    unsigned long long timeout_ns;
 };
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
@@ -114,8 +115,12 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double *__re
     if ((int)threadIdx.x < x.nranks) {   // one polling thread per source rank, all on local memory
         const unsigned long long *flag = reinterpret_cast<const unsigned long long *>(local + XCHG_FLAG_OFF) + threadIdx.x;
         const unsigned long long t0 = global_ns();
+        // a peer that never shows up costs ONE timeout: once the flag is up, this and every later exchange of the
+        // call fall straight through (the results are garbage from there on; xchg_check turns the flag into the
+        // call's error and puts the context's communicator in a failed state)
         while (ld_acquire_sys(flag) < x.seq) {
-            if (global_ns() - t0 > 10000000000ull) { *x.err = 1; break; }
+            if (*reinterpret_cast<volatile int *>(x.err)) break;
+            if (global_ns() - t0 > x.timeout_ns) { *reinterpret_cast<volatile int *>(x.err) = 1; break; }
         }
     }
     __syncthreads();
@@ -135,12 +140,23 @@ int launch_reduce_partials(plsb_ctx *c, const double *part, int64_t ld, int nb, 
                            bool across_ranks) {
     const unsigned grid = (unsigned)ceil_div(len, 32);
     XchgArgs x{};
+    if (across_ranks && c->xchg.failed) {
+        set_error("the communicator of this context is in a failed state (an earlier peer all-reduce timed out): "
+                  "destroy the contexts and create them again");
+        return PLSB_ERR_NCCL;
+    }
     const bool fused = across_ranks && c->nranks > 1 && c->xchg.ready && len <= PLSB_XCHG_LEN && grid <= (unsigned)c->sm_count;
     if (fused) {
         x.rank = c->rank; x.nranks = c->nranks; x.seq = ++c->xchg.seq;
         for (int r = 0; r < c->nranks; ++r) x.area[r] = c->xchg.peer[r];
         x.counter = reinterpret_cast<unsigned *>(c->xchg.base + XCHG_CTR_OFF);
         x.err = reinterpret_cast<int *>(c->xchg.base + XCHG_ERR_OFF);
+        static const unsigned long long tmo = [] {
+            const char *e = getenv("PLSB_XCHG_TIMEOUT_MS");
+            const long long ms = e ? atoll(e) : 0;
+            return (unsigned long long)(ms > 0 ? ms : 10000) * 1000000ull;
+        }();
+        x.timeout_ns = tmo;
     }
     {
         ProfScope ps(c, PLSB_PROF_REDUCE);
@@ -221,6 +237,10 @@ int xchg_check(plsb_ctx *c) {
     int err = 0;
     PLSB_CUDA(cudaMemcpy(&err, c->xchg.base + XCHG_ERR_OFF, sizeof(int), cudaMemcpyDeviceToHost));
     if (err) {
+        // The ranks no longer agree on the exchange number and their results are garbage: no further sharded
+        // call may run on this communicator.  The flag itself is cleared so that the report is made once.
+        c->xchg.failed = true;
+        cudaMemset(c->xchg.base + XCHG_ERR_OFF, 0, sizeof(int));
         set_error("peer all-reduce timed out: a rank of the communicator did not reach the exchange");
         return PLSB_ERR_NCCL;
     }

@@ -119,7 +119,7 @@ int ensure_part(plsb_ctx *c, size_t bytes) {
 }
 
 ProfScope::ProfScope(plsb_ctx *ctx, int slot) : c(ctx) {
-    if (!c->prof || (c->prof == 2 && slot != PLSB_PROF_FIT_TOTAL)) return;
+    if (slot < 0 || !c->prof || (c->prof == 2 && slot != PLSB_PROF_FIT_TOTAL)) return;
     plsb_ctx::Pending p;
     p.slot = slot;
     for (cudaEvent_t *e : {&p.a, &p.b}) {
@@ -150,6 +150,9 @@ static int prof_drain(plsb_ctx *c) {
     return PLSB_OK;
 }
 
+static std::atomic<int> g_live_ctx{0};
+int live_contexts() { return g_live_ctx.load(std::memory_order_relaxed); }
+
 void ctx_retain(plsb_ctx *c) { c->refs.fetch_add(1, std::memory_order_relaxed); }
 
 void ctx_release(plsb_ctx *c) {
@@ -166,6 +169,8 @@ void ctx_release(plsb_ctx *c) {
     if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
     for (int i = 0; i < 4; ++i) if (c->xfer_ev[i]) cudaEventDestroy(c->xfer_ev[i]);
     if (c->col_ev) cudaEventDestroy(c->col_ev);
+    hstage_release(c);
+    g_live_ctx.fetch_sub(1, std::memory_order_relaxed);
     delete c;
 }
 
@@ -211,6 +216,7 @@ int plsb_ctx_create(int device, plsb_ctx_t *out) {
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess)
             cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
+    g_live_ctx.fetch_add(1, std::memory_order_relaxed);
     *out = c;
     return PLSB_OK;
 }
@@ -262,6 +268,14 @@ int plsb_comm_init(plsb_ctx_t c, int rank, int nranks, const void *id128) {
     c->nranks = nranks;
     // peer-memory exchange area for the in-kernel all-reduce (falls back to NCCL per call if it cannot be set up)
     PLSB_TRY(xchg_setup(c, host_allgather));
+    return PLSB_OK;
+}
+
+int plsb_comm_info(plsb_ctx_t c, int *rank, int *nranks, int *peer_exchange) {
+    PLSB_ARG(c, "ctx is null");
+    if (rank) *rank = c->rank;
+    if (nranks) *nranks = c->nranks;
+    if (peer_exchange) *peer_exchange = (c->nranks > 1 && c->xchg.ready && !c->xchg.failed) ? 1 : 0;
     return PLSB_OK;
 }
 

@@ -130,10 +130,20 @@ __device__ __forceinline__ void block_sum_vec(double (&v)[NV], double *red /* [C
 #ifndef PLSB_CV_MINB
 #define PLSB_CV_MINB 4
 #endif
+// shared state of the fused kernel: what it uses of StepSmem, sized for ITS M <= MM (StepSmem's Gram and eigenvector
+// matrices are 32 x 32: 16 KB of the 20 KB — shared memory a co-resident GEMM CTA of the other wave cannot spare)
+template <int MM>
+struct FusedSmem {
+    double q[MM];
+    double c[256];
+    double gram[MM * MM];
+    double V[MM * MM];
+};
+
 template <int MM>
 __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT : 1) cv_fold_fused_kernel(const CvArgs v) {
     constexpr int NP = MM * (MM + 1) / 2;
-    __shared__ StepSmem<CV_FNT> sh;
+    __shared__ FusedSmem<MM> sh;
     __shared__ double red[(CV_FNT / 32 + 1) * (NP > MM ? NP : MM)];
     __shared__ double qe[MM];
     const int tid = threadIdx.x;
@@ -427,12 +437,19 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         }
     }
 
+    // the full cross products: taken from the data set when its upload built them under the transfer (dataset.cu)
     const int64_t ldg = round_up(K, 2);
-    PLSB_TRY(G.alloc((size_t)K * ldg * 8));
-    PLSB_CUDA(cudaMemsetAsync(G.p, 0, (size_t)K * ldg * 8, c->stream));
-    PLSB_TRY(S0.alloc((size_t)M * ldk * 8));
-    PLSB_TRY(launch_xtx(c, ds, G.d(), ldg));
-    PLSB_TRY(launch_xty_pass(c, ds, S0.d()));
+    const double *Gfull = nullptr, *S0full = nullptr;
+    if (ds->G && ds->S0 && ds->gram_valid && ds->ldg == ldg) {
+        Gfull = ds->G; S0full = ds->S0;
+    } else {
+        PLSB_TRY(G.alloc((size_t)K * ldg * 8));
+        PLSB_CUDA(cudaMemsetAsync(G.p, 0, (size_t)K * ldg * 8, c->stream));
+        PLSB_TRY(S0.alloc((size_t)M * ldk * 8));
+        PLSB_TRY(launch_xtx(c, ds, G.d(), ldg));
+        PLSB_TRY(launch_xty_pass(c, ds, S0.d()));
+        Gfull = G.d(); S0full = S0.d();
+    }
 
     // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles.  At most 4736
     // folds = 37 column tiles of the batched GEMM: with K = 4096 (32 row tiles) that is 1184 CTAs = 8 full waves of
@@ -453,7 +470,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     PLSB_TRY(U.alloc((size_t)F * ts * 8));
 
     CvArgs v{};
-    v.X = ds->X; v.Y = ds->Y; v.S0 = S0.d(); v.test_idx = (const int64_t *)idx.p;
+    v.X = ds->X; v.Y = ds->Y; v.S0 = S0full; v.test_idx = (const int64_t *)idx.p;
     v.S = S.d(); v.P = P.d(); v.R = R.d(); v.w = w.d(); v.Gr = Gr.d(); v.U = U.d(); v.E = Ed.d();
     v.rows_local = rows_local; v.K = (int)K; v.ldk = (int)ldk; v.ldm = (int)ds->ldm; v.M = (int)M; v.A = (int)A;
     v.ts = (int)ts;
@@ -465,7 +482,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         for (int a = -1; a < (int)A; ++a) {
             v.a = a;
             if (a >= 0)  // Gr[f][:] = (X'X) r_f for the whole wave: one DMMA GEMM
-                PLSB_TRY(launch_gemm_atb(c, G.d(), ldg, R.d() + (size_t)a * ldk, A * ldk, K, (int)K, nf, Gr.d(), ldk,
+                PLSB_TRY(launch_gemm_atb(c, Gfull, ldg, R.d() + (size_t)a * ldk, A * ldk, K, (int)K, nf, Gr.d(), ldk,
                                          false, true, true, PLSB_PROF_CV_GEMM));
             {
                 ProfScope ps(c, PLSB_PROF_CV_FOLD);

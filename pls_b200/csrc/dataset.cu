@@ -1,9 +1,107 @@
 // pls_b200/csrc/dataset.cu — device-resident data sets: the role of Model's `_X,_Y` copies
 // (reference src/pls.cpp:344, include/PLS/pls.h:251), kept in HBM in the row-major layout the
 // streaming passes want.
+#include <string.h>
+
+#include <thread>
+
+#include "host_pool.h"
 #include "internal.h"
 
 namespace plsb {
+
+// ---- pageable host sources ------------------------------------------------------------------------------------------
+// cudaMemcpy from pageable memory is staged by the driver through its own bounce buffers on ONE thread (6-12 GB/s: a
+// fifth of PCIe 5 x16).  A caller of the drop-in API hands over an ordinary Eigen matrix (pls.cpp:340-353), so the
+// staging is done here instead: a pool of host threads packs block i+1 into a pinned write-combined buffer while the
+// copy engine sends block i, three buffers deep.  Pinned (or registered) sources skip it and are copied in place.
+static bool host_is_pageable(const void *p) {
+    cudaPointerAttributes a{};
+    const cudaError_t e = cudaPointerGetAttributes(&a, p);
+    cudaGetLastError();
+    return e != cudaSuccess || a.type == cudaMemoryTypeUnregistered;
+}
+
+static int hstage_ensure(plsb_ctx *c, size_t bytes) {
+    plsb_ctx::HostStage &h = c->hstage;
+    if (!h.pool) {
+        int n = 0;
+        if (const char *e = getenv("PLSB_PACK_THREADS")) n = atoi(e);
+        if (n <= 0) {
+            const int hw = (int)std::thread::hardware_concurrency(), live = live_contexts() > 0 ? live_contexts() : 1;
+            n = hw / live;
+            if (n > 16) n = 16;
+            if (n < 2) n = 2;
+        }
+        h.pool = new HostPool(n);
+    }
+    if (bytes <= h.bytes) return PLSB_OK;
+    for (int i = 0; i < 3; ++i) {
+        if (h.done[i]) cudaEventSynchronize(h.done[i]);
+        if (h.buf[i]) cudaFreeHost(h.buf[i]);
+        h.buf[i] = nullptr;
+    }
+    h.bytes = 0;
+    bytes = (size_t)round_up((int64_t)bytes, 1 << 20);
+    const char *wc = getenv("PLSB_STAGE_WC");
+    const unsigned flags = (wc && *wc == '0') ? cudaHostAllocDefault : cudaHostAllocWriteCombined;
+    for (int i = 0; i < 3; ++i) {
+        PLSB_CUDA(cudaHostAlloc((void **)&h.buf[i], bytes, flags));
+        if (!h.done[i]) PLSB_CUDA(cudaEventCreateWithFlags(&h.done[i], cudaEventDisableTiming));
+    }
+    h.bytes = bytes;
+    return PLSB_OK;
+}
+
+void hstage_release(plsb_ctx *c) {
+    plsb_ctx::HostStage &h = c->hstage;
+    for (int i = 0; i < 3; ++i) {
+        if (h.done[i]) cudaEventDestroy(h.done[i]);
+        if (h.buf[i]) cudaFreeHost(h.buf[i]);
+    }
+    delete h.pool;
+    h = plsb_ctx::HostStage();
+}
+
+// dst (packed, segment j at j * seg) <- nseg segments of `seg` bytes, segment j at src + j * stride; the bytes are
+// dealt to the pool's threads in contiguous, cache-line-aligned ranges of the destination
+static void pack_segments(HostPool &pool, char *dst, const char *src, size_t seg, size_t stride, size_t nseg) {
+    const size_t total = seg * nseg;
+    pool.run([&](int t, int n) {
+        size_t a = total / (size_t)n * (size_t)t, b = (t + 1 == n) ? total : total / (size_t)n * (size_t)(t + 1);
+        a &= ~(size_t)63;
+        if (t + 1 < n) b &= ~(size_t)63;
+        while (a < b) {
+            const size_t j = a / seg, off = a % seg;
+            const size_t len = seg - off < b - a ? seg - off : b - a;
+            memcpy(dst + a, src + j * stride + off, len);
+            a += len;
+        }
+    });
+}
+
+static bool stage_wanted(const void *src, size_t total_bytes) {
+    const char *e = getenv("PLSB_NO_STAGE");
+    if (e && *e == '1') return false;
+    return total_bytes >= ((size_t)8 << 20) && host_is_pageable(src);
+}
+
+// One block of a host column-major matrix (nseg column segments of nr rows, packed column-major with ld = nr) to
+// the device buffer `buf` on the copy stream: straight from a pinned source, or packed by the host threads first.
+static cudaError_t send_block(plsb_ctx *c, bool staged, int64_t i, double *buf, const double *src, int64_t lds, int64_t nr,
+                              int64_t nseg) {
+    if (!staged)
+        return cudaMemcpy2DAsync(buf, (size_t)nr * 8, src, (size_t)lds * 8, (size_t)nr * 8, (size_t)nseg,
+                                 cudaMemcpyHostToDevice, c->copy_stream);
+    plsb_ctx::HostStage &h = c->hstage;
+    const int hb = (int)(i % 3);
+    cudaError_t e = cudaEventSynchronize(h.done[hb]);   // the copy that read this buffer three blocks ago
+    if (e != cudaSuccess) return e;
+    pack_segments(*h.pool, h.buf[hb], (const char *)src, (size_t)nr * 8, (size_t)lds * 8, (size_t)nseg);
+    e = cudaMemcpyAsync(buf, h.buf[hb], (size_t)nr * 8 * (size_t)nseg, cudaMemcpyHostToDevice, c->copy_stream);
+    if (e == cudaSuccess) e = cudaEventRecord(h.done[hb], c->copy_stream);
+    return e;
+}
 
 int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst, int64_t ldd,
                     bool src_on_device) {
@@ -15,6 +113,8 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
     int64_t kc = (int64_t)(128u << 20) / (rows * 8);
     if (kc < 1) kc = 1;
     if (kc > cols) kc = cols;
+    const bool staged = stage_wanted(src, (size_t)rows * cols * 8);
+    if (staged) PLSB_TRY(hstage_ensure(c, (size_t)rows * kc * 8));
     double *stage = nullptr;
     PLSB_TRY(dev_alloc(c, (void **)&stage, (size_t)2 * rows * kc * sizeof(double)));
     cudaEvent_t *copied = c->xfer_ev, *moved = c->xfer_ev + 2;
@@ -27,9 +127,7 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
         const int b = (int)(i & 1);
         double *buf = stage + (size_t)b * rows * kc;
         e = cudaStreamWaitEvent(c->copy_stream, moved[b], 0);  // block i-2 has left this buffer
-        if (e == cudaSuccess)
-            e = cudaMemcpy2DAsync(buf, (size_t)rows * 8, src + c0 * lds, (size_t)lds * 8, (size_t)rows * 8, (size_t)nc,
-                                  cudaMemcpyHostToDevice, c->copy_stream);
+        if (e == cudaSuccess) e = send_block(c, staged, i, buf, src + c0 * lds, lds, rows, nc);
         if (e == cudaSuccess) e = cudaEventRecord(copied[b], c->copy_stream);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, copied[b], 0);
         if (e != cudaSuccess) break;
@@ -47,7 +145,7 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
 
 // Host column-major X -> device row-major X in ROW blocks (strided 2-D H2D copies on the copy stream, two staging
 // buffers), and while block i+1 crosses PCIe the tensor cores add block i's contribution to XX = X'X (SYRK, DMMA).
-// The upload is PCIe-bound (~55 GB/s) and X'X needs N*K*(K+128) flops at ~28 TFLOP/s: for K <= ~3000 the whole
+// The upload is PCIe-bound (~55 GB/s) and X'X needs N*K*(K+128) flops at ~36 TFLOP/s: for K <= ~3000 the whole
 // cross-product build hides under the transfer, and a fit that follows needs no further pass over X except the
 // one that forms the scores (fit.cu).  SURVEY 8(f)-3: chunked H2D overlapped with the cross-product pass.
 static bool gram_on_upload(int64_t N, int64_t K) {
@@ -67,6 +165,8 @@ static int upload_rows_with_gram(plsb_ctx *c, const double *src, int64_t lds, pl
     int64_t nb = (int64_t)(128u << 20) / (K * 8) / 1024 * 1024;
     if (nb < 1024) nb = 1024;
     if (nb > N) nb = N;
+    const bool staged = stage_wanted(src, (size_t)N * K * 8);
+    if (staged) PLSB_TRY(hstage_ensure(c, (size_t)nb * K * 8));
     double *stage = nullptr;
     PLSB_TRY(dev_alloc(c, (void **)&stage, (size_t)2 * nb * K * sizeof(double)));
     cudaEvent_t *copied = c->xfer_ev, *moved = c->xfer_ev + 2;
@@ -80,8 +180,7 @@ static int upload_rows_with_gram(plsb_ctx *c, const double *src, int64_t lds, pl
         double *buf = stage + (size_t)b * nb * K;
         e = cudaStreamWaitEvent(c->copy_stream, moved[b], 0);
         if (e == cudaSuccess)   // K column segments of nr rows each, packed column-major (ld = nr)
-            e = cudaMemcpy2DAsync(buf, (size_t)nr * 8, src + r0, (size_t)lds * 8, (size_t)nr * 8, (size_t)K,
-                                  cudaMemcpyHostToDevice, c->copy_stream);
+            e = send_block(c, staged, i, buf, src + r0, lds, nr, K);
         if (e == cudaSuccess) e = cudaEventRecord(copied[b], c->copy_stream);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(c->stream, copied[b], 0);
         if (e != cudaSuccess) break;
@@ -192,6 +291,40 @@ int plsb_dataset_destroy(plsb_dataset_t ds) {
     plsb_ctx *c = ds->ctx;
     delete ds;
     ctx_release(c);
+    return PLSB_OK;
+}
+int plsb_dataset_concat(plsb_ctx_t c, int64_t nparts, const plsb_dataset_t *parts, plsb_dataset_t *out) {
+    PLSB_ARG(c && parts && out && nparts >= 1, "null argument");
+    int64_t N = 0;
+    for (int64_t i = 0; i < nparts; ++i) {
+        PLSB_ARG(parts[i], "part %lld is null", (long long)i);
+        PLSB_ARG(parts[i]->K == parts[0]->K && parts[i]->M == parts[0]->M, "parts disagree on K or M");
+        N += parts[i]->N;
+    }
+    plsb_dataset *ds = nullptr;
+    PLSB_TRY(dataset_alloc(c, N, parts[0]->K, parts[0]->M, &ds));
+    // rows are contiguous in the row-major layout: one copy per part and matrix (device to device; peer copies over
+    // NVLink when the part lives on another GPU).  Padding columns are copied with the rows.
+    int rc = PLSB_OK;
+    int64_t r0 = 0;
+    for (int64_t i = 0; i < nparts && rc == PLSB_OK; ++i) {
+        const plsb_dataset *p = parts[i];
+        cudaError_t e = cudaSetDevice(p->ctx->device);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(p->ctx->stream);     // the part's own work has finished
+        if (e == cudaSuccess) e = cudaSetDevice(c->device);
+        if (e == cudaSuccess && p->N > 0)
+            e = cudaMemcpyPeerAsync(ds->X + r0 * ds->ldk, c->device, p->X, p->ctx->device, (size_t)p->N * ds->ldk * 8, c->stream);
+        if (e == cudaSuccess && p->N > 0)
+            e = cudaMemcpyPeerAsync(ds->Y + r0 * ds->ldm, c->device, p->Y, p->ctx->device, (size_t)p->N * ds->ldm * 8, c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "dataset concat", __FILE__, __LINE__);
+        r0 += p->N;
+    }
+    if (rc == PLSB_OK) {
+        cudaError_t e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = cuda_fail(e, "dataset concat", __FILE__, __LINE__);
+    }
+    if (rc != PLSB_OK) { plsb_dataset_destroy(ds); return rc; }
+    *out = ds;
     return PLSB_OK;
 }
 int plsb_dataset_shape(plsb_dataset_t ds, int64_t *N, int64_t *K, int64_t *M) {

@@ -190,8 +190,13 @@ __device__ __forceinline__ void gt_mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-template <bool B_NMAJOR, int CW>
-__global__ void __launch_bounds__((CW + 1) * 32) __maxnreg__(CW == 8 ? 168 : 96) dmma_tma_kernel(const GemmArgs g) {
+// SELF = false: CW consumer warps + one producer warp (warp CW).  SELF = true: no producer warp — the CW consumer warps
+// take turns (warp kt mod CW issues the copies of k-tile kt + 2 at the top of iteration kt).  A CTA of 8 warps x 168
+// registers leaves a quarter of the SM's register file and 16 KB of its shared memory free, so that a memory-bound kernel
+// of another stream (the per-fold kernel of the other CV wave, cv.cu) can be co-resident and use the HBM bandwidth this
+// tensor-bound kernel leaves idle; 9 warps are allocated as 12 and take the whole register file.
+template <bool B_NMAJOR, int CW, bool SELF>
+__global__ void __launch_bounds__((CW + (SELF ? 0 : 1)) * 32) __maxnreg__(CW == 8 ? 168 : 96) dmma_tma_kernel(const GemmArgs g) {
     extern __shared__ __align__(128) char smem[];
     constexpr int STAGE = gt_stage_bytes(B_NMAJOR);
     constexpr int WM = GM_BM / (CW / 4), MI = WM / 8;
@@ -216,39 +221,42 @@ __global__ void __launch_bounds__((CW + 1) * 32) __maxnreg__(CW == 8 ? 168 : 96)
     }
     __syncthreads();
 
-    if (warp == CW) {
-        // ---- producer: bulk copies of the valid part of each tile row; rows / columns past the matrix edge are
-        // never copied (the consumers mask the k tail, and out-of-range output rows / columns are discarded) ----
-        int a_cols = g.M - m_base; a_cols = a_cols > GM_BM ? GM_BM : (a_cols + 1) & ~1;
-        int b_cols = g.N - n_base; b_cols = b_cols > GM_BN ? GM_BN : b_cols;          // n-major: rows of the B tile
-        const int b_cols2 = (b_cols + 1) & ~1;                                       // k-major: doubles per k-row
-        for (int kt = 0; kt < nk; ++kt) {
-            const int s = kt % GT_STAGES;
-            if (kt >= GT_STAGES) mbar_wait(&empty[s], (uint32_t)(((kt / GT_STAGES) - 1) & 1));
-            const int64_t k0 = k_begin + (int64_t)kt * GT_BK;
-            const int kv = (int)(k_end - k0 < GT_BK ? k_end - k0 : GT_BK);
-            const int kv2 = (kv + 1) & ~1;
-            char *sa = smem + (size_t)s * STAGE, *sb = sa + GT_A_BYTES;
-            const uint32_t bytes = (uint32_t)kv * (uint32_t)a_cols * 8u +
-                                   (B_NMAJOR ? (uint32_t)b_cols * (uint32_t)kv2 * 8u : (uint32_t)kv * (uint32_t)b_cols2 * 8u);
-            if (lane == 0) mbar_arrive_expect_tx(&full[s], bytes);
-            __syncwarp();
-            if (lane < kv) {
-                bulk_g2s(sa + (size_t)lane * GT_LD * 8, g.A + (k0 + lane) * g.lda + m_base, (uint32_t)a_cols * 8u, &full[s]);
-                if (!B_NMAJOR)
-                    bulk_g2s(sb + (size_t)lane * GT_LD * 8, g.B + (k0 + lane) * g.ldb + n_base, (uint32_t)b_cols2 * 8u, &full[s]);
-            }
-            if (B_NMAJOR) {
+    // ---- producer step (one whole warp): bulk copies of the valid part of each tile row of k-tile kt; rows / columns
+    // past the matrix edge are never copied (the consumers mask the k tail, and out-of-range output rows / columns are
+    // discarded) ----
+    int a_cols = g.M - m_base; a_cols = a_cols > GM_BM ? GM_BM : (a_cols + 1) & ~1;
+    int b_cols = g.N - n_base; b_cols = b_cols > GM_BN ? GM_BN : b_cols;          // n-major: rows of the B tile
+    const int b_cols2 = (b_cols + 1) & ~1;                                       // k-major: doubles per k-row
+    auto produce = [&](int kt) {
+        const int s = kt % GT_STAGES;
+        if (kt >= GT_STAGES) mbar_wait(&empty[s], (uint32_t)(((kt / GT_STAGES) - 1) & 1));
+        const int64_t k0 = k_begin + (int64_t)kt * GT_BK;
+        const int kv = (int)(k_end - k0 < GT_BK ? k_end - k0 : GT_BK);
+        const int kv2 = (kv + 1) & ~1;
+        char *sa = smem + (size_t)s * STAGE, *sb = sa + GT_A_BYTES;
+        const uint32_t bytes = (uint32_t)kv * (uint32_t)a_cols * 8u +
+                               (B_NMAJOR ? (uint32_t)b_cols * (uint32_t)kv2 * 8u : (uint32_t)kv * (uint32_t)b_cols2 * 8u);
+        if (lane == 0) mbar_arrive_expect_tx(&full[s], bytes);
+        __syncwarp();
+        if (lane < kv) {
+            bulk_g2s(sa + (size_t)lane * GT_LD * 8, g.A + (k0 + lane) * g.lda + m_base, (uint32_t)a_cols * 8u, &full[s]);
+            if (!B_NMAJOR)
+                bulk_g2s(sb + (size_t)lane * GT_LD * 8, g.B + (k0 + lane) * g.ldb + n_base, (uint32_t)b_cols2 * 8u, &full[s]);
+        }
+        if (B_NMAJOR) {
 #pragma unroll
-                for (int i = 0; i < GM_BN / 32; ++i) {
-                    const int n = lane + 32 * i;
-                    if (n < b_cols)
-                        bulk_g2s(sb + (size_t)n * GT_LDBN * 8, g.B + (int64_t)(n_base + n) * g.ldb + k0, (uint32_t)kv2 * 8u, &full[s]);
-                }
+            for (int i = 0; i < GM_BN / 32; ++i) {
+                const int n = lane + 32 * i;
+                if (n < b_cols)
+                    bulk_g2s(sb + (size_t)n * GT_LDBN * 8, g.B + (int64_t)(n_base + n) * g.ldb + k0, (uint32_t)kv2 * 8u, &full[s]);
             }
         }
+    };
+    if (!SELF && warp == CW) {
+        for (int kt = 0; kt < nk; ++kt) produce(kt);
         return;
     }
+    if (SELF && warp < GT_STAGES - 1 && warp < nk) produce(warp);     // prologue: tiles 0 and 1 by warps 0 and 1
 
     // ---- consumers ------------------------------------------------------------------------------------------------
     double acc[MI][4][2];
@@ -260,6 +268,7 @@ __global__ void __launch_bounds__((CW + 1) * 32) __maxnreg__(CW == 8 ? 168 : 96)
     const int fk = lane & 3, fr = lane >> 2;
     for (int kt = 0; kt < nk; ++kt) {
         const int s = kt % GT_STAGES;
+        if (SELF && warp == (kt % CW) && kt + GT_STAGES - 1 < nk) produce(kt + GT_STAGES - 1);   // the stage freed by tile kt - 1
         mbar_wait(&full[s], (uint32_t)((kt / GT_STAGES) & 1));
         const double *as = reinterpret_cast<const double *>(smem + (size_t)s * STAGE) + fk * GT_LD + wm + fr;
         const double *bs = reinterpret_cast<const double *>(smem + (size_t)s * STAGE + GT_A_BYTES) +
@@ -347,9 +356,11 @@ __global__ void __launch_bounds__(256) gemm_reduce_kernel(const GemmArgs g, doub
 // C (M x N, row-major, ldc) = A' B.  syrk: A == B, M == N, C symmetric.  b_nmajor: B given as N x Kd.
 // transC: store C transposed (N x M, row-major).
 int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
-                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate) {
+                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate,
+                    GemmLane *lane) {
     if (M == 0 || N == 0) return PLSB_OK;
     PLSB_ARG((lda % 2) == 0 && (ldb % 2) == 0, "gemm: leading dimensions must be even");
+    cudaStream_t st = lane ? lane->stream : c->stream;
     GemmArgs g{};
     g.A = A; g.lda = lda; g.B = B; g.ldb = ldb; g.Kd = Kd; g.M = M; g.N = N; g.syrk = syrk ? 1 : 0;
     g.transC = transC ? 1 : 0; g.C = C; g.ldc = ldc; g.accum = accumulate ? 1 : 0;
@@ -374,34 +385,50 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
     const bool direct = g.splitk == 1 && !syrk && !accumulate;
     if (!direct) {
         const size_t pbytes = (size_t)g.splitk * g.ntiles * GM_BM * GM_BN * sizeof(double);
-        PLSB_TRY(ensure_part(c, pbytes));
-        g.part = c->part;
+        if (lane) {     // a lane of a multi-stream caller owns its scratch (the context's belongs to c->stream)
+            if (pbytes > lane->part_bytes) {
+                if (lane->part) cudaFreeAsync(lane->part, st);
+                lane->part = nullptr; lane->part_bytes = 0;
+                PLSB_CUDA(cudaMallocAsync((void **)&lane->part, pbytes, st));
+                lane->part_bytes = pbytes;
+            }
+            g.part = lane->part;
+        } else {
+            PLSB_TRY(ensure_part(c, pbytes));
+            g.part = c->part;
+        }
     }
-    static const int variant = [] {   // A/B switches: PLSB_GEMM_V1=1 the cp.async kernel, PLSB_GEMM_CW=16 sixteen 32x32 consumer warps
+    // A/B switches: PLSB_GEMM_V1=1 the cp.async kernel, PLSB_GEMM_CW=16 sixteen 32x32 consumer warps, PLSB_GEMM_SELF=0/1
+    // forces the producer-warp / self-fed pipeline (default: self-fed for lanes, i.e. when another stream may co-run)
+    static const int variant = [] {
         const char *v1 = getenv("PLSB_GEMM_V1"), *cw = getenv("PLSB_GEMM_CW");
         if (v1 && *v1 == '1') return 1;
         return (cw && atoi(cw) == 16) ? 16 : 8;
     }();
+    static const int self_env = [] { const char *e = getenv("PLSB_GEMM_SELF"); return e ? atoi(e) : -1; }();
+    const bool self = self_env >= 0 ? self_env != 0 : lane != nullptr;
     if (b_nmajor) PLSB_ARG(ldb >= round_up(Kd, 2), "gemm: an n-major B needs ldb >= Kd rounded up to even");
     if (variant == 1) {
         const size_t smem = (size_t)GM_STAGES * (GM_BK * GM_LD + (b_nmajor ? GM_BS_NMAJOR : GM_BS_KMAJOR)) * sizeof(double);
         auto kern = b_nmajor ? dmma_atb_kernel<true> : dmma_atb_kernel<false>;
         PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ProfScope ps(c, prof_slot);
-        kern<<<(unsigned)(g.ntiles * g.splitk), GM_NT, smem, c->stream>>>(g);
+        ProfScope ps(c, lane ? -1 : prof_slot);
+        kern<<<(unsigned)(g.ntiles * g.splitk), GM_NT, smem, st>>>(g);
     } else {
         const size_t smem = (size_t)GT_STAGES * gt_stage_bytes(b_nmajor) + 2 * GT_STAGES * sizeof(uint64_t) + 16;
-        void (*kern)(const GemmArgs) =
-            variant == 16 ? (b_nmajor ? dmma_tma_kernel<true, 16> : dmma_tma_kernel<false, 16>)
-                          : (b_nmajor ? dmma_tma_kernel<true, 8> : dmma_tma_kernel<false, 8>);
+        void (*kern)(const GemmArgs);
+        unsigned threads;
+        if (variant == 16) { kern = b_nmajor ? dmma_tma_kernel<true, 16, false> : dmma_tma_kernel<false, 16, false>; threads = 17 * 32; }
+        else if (self) { kern = b_nmajor ? dmma_tma_kernel<true, 8, true> : dmma_tma_kernel<false, 8, true>; threads = 8 * 32; }
+        else { kern = b_nmajor ? dmma_tma_kernel<true, 8, false> : dmma_tma_kernel<false, 8, false>; threads = 9 * 32; }
         PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        ProfScope ps(c, prof_slot);
-        kern<<<(unsigned)(g.ntiles * g.splitk), (variant + 1) * 32, smem, c->stream>>>(g);
+        ProfScope ps(c, lane ? -1 : prof_slot);
+        kern<<<(unsigned)(g.ntiles * g.splitk), threads, smem, st>>>(g);
     }
     PLSB_CUDA(cudaGetLastError());
     c->launches += 1;
     if (!direct) {
-        gemm_reduce_kernel<<<(unsigned)g.ntiles, 256, 0, c->stream>>>(g, C, ldc);
+        gemm_reduce_kernel<<<(unsigned)g.ntiles, 256, 0, st>>>(g, C, ldc);
         PLSB_CUDA(cudaGetLastError());
         c->launches += 1;
     }

@@ -5,6 +5,8 @@
 
 #include "common.cuh"
 
+namespace plsb { class HostPool; }
+
 #define PLSB_MAX_RANKS 16
 #define PLSB_XCHG_LEN 8192          /* doubles per exchange slot */
 
@@ -31,11 +33,21 @@ struct plsb_ctx {
     // peer-memory exchange area for the in-kernel all-reduce of the per-component [g | tt] vector (allreduce.cu)
     struct Xchg {
         bool ready = false;
+        bool failed = false;            // an exchange timed out: sharded calls on this context are refused from now on
         char *base = nullptr;           // this rank's area (cudaMalloc: IPC-exportable)
         char *peer[PLSB_MAX_RANKS] = {nullptr};
         bool ipc_opened[PLSB_MAX_RANKS] = {false};
         unsigned long long seq = 0;     // exchanges done so far (identical on every rank)
     } xchg;
+    // Pageable host sources (an ordinary Eigen matrix, a numpy array) reach the copy engine through a ring of three
+    // pinned, write-combined staging buffers that a small pool of host threads fills (dataset.cu: staged uploads);
+    // allocated on first use, kept for the life of the context.
+    struct HostStage {
+        char *buf[3] = {nullptr, nullptr, nullptr};
+        size_t bytes = 0;
+        cudaEvent_t done[3] = {nullptr, nullptr, nullptr};   // "the H2D copy that read buf[i] has finished"
+        plsb::HostPool *pool = nullptr;
+    } hstage;
     // profiling
     int prof = 0;   // 0 off, 1 an event pair around every launch group, 2 only around whole fits (PLSB_PROF_FIT_TOTAL)
     struct Pending { int slot; cudaEvent_t a, b; };
@@ -76,6 +88,8 @@ struct plsb_model {
 
 namespace plsb {
 
+int live_contexts();             // contexts of this process that have not been torn down
+void hstage_release(plsb_ctx *c);  // dataset.cu
 void ctx_retain(plsb_ctx *c);
 void ctx_release(plsb_ctx *c);   // tears the context down when the last reference goes
 int ensure_part(plsb_ctx *c, size_t bytes);
@@ -142,8 +156,12 @@ int launch_step(plsb_ctx *c, const StepArgs &s);
 int launch_symv(plsb_ctx *c, const double *G, int64_t ldg, int K, const double *r, double *out /*ldk+1*/, int ldk);
 
 // ---- FP64 DMMA contraction (gemm.cu) --------------------------------------------------------------
+// `lane`: a caller that keeps several streams busy (the two-wave CV engine) passes the stream to launch on and a
+// split-K scratch of its own; nullptr = the context's stream and scratch.  No profiling events are recorded for lanes.
+struct GemmLane { cudaStream_t stream = nullptr; double *part = nullptr; size_t part_bytes = 0; };
 int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
-                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate = false);
+                    double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate = false,
+                    GemmLane *lane = nullptr);
 // S (component-major A x lds) = X R for row-major X (N x ldk) and component-major R (A x ldk): DMMA (scores.cu)
 int launch_scores(plsb_ctx *c, const double *X, int64_t N, int ldk, const double *R, int A, double *S, int64_t lds);
 int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg);

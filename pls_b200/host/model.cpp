@@ -28,44 +28,42 @@ inline int64_t ld(const Mat2D &m) { return m.rows() > 0 ? (int64_t)m.rows() : 1;
 }  // namespace
 
 // ---- constructors (pls.cpp:323-359) ---------------------------------------------------------------
+// every constructor leaves K x A zero matrices P, W, R and an M x A zero Q behind before any fit runs
+void Model::init_state(size_t num_predictors, size_t num_responses) {
+    assert(A <= num_predictors);
+    for (Mat2Dc *m : {&P, &W, &R}) *m = Mat2Dc::Zero(num_predictors, A);
+    Q = Mat2Dc::Zero(num_responses, A);
+}
+
 Model::Model(const size_t &num_predictors, const size_t &num_responses, const METHOD &algorithm,
              const size_t &max_components)
     : A(max_components), method(algorithm) {
-    assert(max_components <= num_predictors);
-    P.setZero(num_predictors, A);
-    W.setZero(num_predictors, A);
-    R.setZero(num_predictors, A);
-    Q.setZero(num_responses, A);
+    init_state(num_predictors, num_responses);
 }
 
 Model::Model(const size_t &num_predictors, const size_t &num_responses, const METHOD &algorithm)
     : Model(num_predictors, num_responses, algorithm, num_predictors) {}
 
+// The fitting constructor: the reference copies X, Y into `_X,_Y` and fits (pls.cpp:340-353).  Here the copy is the
+// upload: the data set the fit creates in HBM is kept as the model's own copy of its training data (cv_LOO / cv_LSO
+// run from it), and no second copy is made in host memory.
 Model::Model(const Mat2D &X, const Mat2D &Y, const METHOD &algorithm, const size_t &max_components)
-    : _X(X), _Y(Y), A(max_components), method(algorithm) {
-    assert(max_components <= static_cast<size_t>(_X.cols()));
-    assert(_X.rows() != 0);
-    assert(_X.rows() == _Y.rows());
-    P.setZero(_X.cols(), A);
-    W.setZero(_X.cols(), A);
-    R.setZero(_X.cols(), A);
-    Q.setZero(_Y.cols(), A);
-    // the device copy of (_X, _Y) made for this fit is kept: cv_LOO / cv_LSO reuse it
+    : A(max_components), method(algorithm) {
+    assert(X.rows() != 0);
+    assert(X.rows() == Y.rows());
+    init_state(X.cols(), Y.cols());
     mirror = std::make_shared<DeviceMirror>();
-    mirror->N = _X.rows(); mirror->K = _X.cols(); mirror->M = _Y.cols();
-    method = algorithm;
-    fit_on(*mirror, _X, _Y, algorithm);
+    mirror->N = X.rows(); mirror->K = X.cols(); mirror->M = Y.cols();
+    fit_on(*mirror, X, Y, algorithm);
 }
 
 Model::Model(const Mat2D &X, const Mat2D &Y, const METHOD &algorithm) : Model(X, Y, algorithm, X.cols()) {}
 
 // ---- fit (pls.cpp:390-437) ------------------------------------------------------------------------
+// A public plsr() refits P, W, R, Q, T on the data it is given and leaves the model's own training data alone, as
+// in the reference (`_X,_Y` are const there): the device copy of foreign data lives for this call only.
 void Model::plsr(const Mat2D &X, const Mat2D &Y, const METHOD &algorithm) {
-    if (X.data() == _X.data() && Y.data() == _Y.data() && mirror) {  // refit on the model's own data
-        fit_on(*mirror, X, Y, algorithm);
-        return;
-    }
-    DeviceMirror scratch;  // foreign data: device copy lives for this call only
+    DeviceMirror scratch;
     scratch.N = X.rows(); scratch.K = X.cols(); scratch.M = Y.cols();
     fit_on(scratch, X, Y, algorithm);
 }
@@ -81,31 +79,33 @@ void Model::fit_on(DeviceMirror &data, const Mat2D &X, const Mat2D &Y, const MET
     if (wantT) Tr.resize(N, A);
     const size_t ndev = e.ndev();
     if (ndev > 1 && N >= e.shard_min_rows) {
-        // row-sharded fit: every GPU streams its rows, K-length partials are all-reduced
+        // row-sharded fit: every GPU streams its rows, K-length partials are all-reduced.  The shards
+        // stay: together they are the model's copy of the training data (cv_* gathers them device to device).
         e.ensure_comm();
-        data.make_shards(X.data(), ld(X), Y.data(), ld(Y));
+        data.load_shards(X.data(), ld(X), Y.data(), ld(Y));
         std::vector<Mat2D> Tpart(ndev);
         e.parallel([&](size_t i) {
             const int64_t rows = data.shard_row0[i + 1] - data.shard_row0[i];
             if (wantT) Tpart[i].resize(rows, A);
             const bool lead = i == 0;  // the K-sized results are replicated: read them from rank 0 only
-            ok(plsb_fit(data.shard[i], (int64_t)A, meth, lead ? Wr.data() : nullptr, lead ? Pr.data() : nullptr,
-                        lead ? Rr.data() : nullptr, lead ? Qr.data() : nullptr, wantT ? Tpart[i].data() : nullptr),
-               "plsb_fit(sharded)");
-        });
+            return plsb_fit(data.shard[i], (int64_t)A, meth, lead ? Wr.data() : nullptr, lead ? Pr.data() : nullptr,
+                            lead ? Rr.data() : nullptr, lead ? Qr.data() : nullptr, wantT ? Tpart[i].data() : nullptr);
+        }, "plsb_fit(sharded)");
         if (wantT)
             for (size_t i = 0; i < ndev; ++i) Tr.middleRows(data.shard_row0[i], Tpart[i].rows()) = Tpart[i];
-        data.drop_shards();
     } else {
-        plsb_dataset_t ds = data.full_on(0, X.data(), ld(X), Y.data(), ld(Y));
-        ok(plsb_fit(ds, (int64_t)A, meth, Wr.data(), Pr.data(), Rr.data(), Qr.data(), wantT ? Tr.data() : nullptr),
+        data.load_full(X.data(), ld(X), Y.data(), ld(Y));
+        ok(plsb_fit(data.full[0], (int64_t)A, meth, Wr.data(), Pr.data(), Rr.data(), Qr.data(), wantT ? Tr.data() : nullptr),
            "plsb_fit");
     }
     W = as_complex(Wr);
     P = as_complex(Pr);
     R = as_complex(Rr);
     Q = as_complex(Qr);
-    if (wantT) T = as_complex(Tr);  // KERNEL_TYPE2 leaves T as it was (pls.cpp:394, 434)
+    if (wantT) {  // KERNEL_TYPE2 leaves T as it was (pls.cpp:394, 434)
+        T.resize(N, A);
+        Engine::widen(Tr.data(), T.data(), (size_t)N * A);
+    }
 }
 
 // ---- prediction helpers (pls.cpp:439-467) ---------------------------------------------------------
@@ -121,10 +121,10 @@ std::vector<int64_t> row_shards(Engine &e, int64_t rows) {
     return b;
 }
 template <typename Fn>
-void over_shards(Engine &e, const std::vector<int64_t> &b, Fn fn) {
+void over_shards(Engine &e, const std::vector<int64_t> &b, const char *where, Fn fn) {   // fn(i) returns a plsb status
     const size_t g = b.size() - 1;
-    if (g == 1) { fn(0); return; }
-    e.parallel([&](size_t i) { if (i < g) fn(i); });
+    if (g == 1) { ok(fn(0), where); return; }
+    e.parallel([&](size_t i) { return i < g ? fn(i) : (int)PLSB_OK; }, where);
 }
 }  // namespace
 
@@ -137,11 +137,10 @@ const Mat2Dc Model::scores(const Mat2D &X_new, const size_t comp) const {
     if (comp > 0) {
         const std::vector<int64_t> b = row_shards(e, X_new.rows());
         std::vector<Mat2D> part(b.size() - 1);
-        over_shards(e, b, [&](size_t i) {
+        over_shards(e, b, "plsb_scores", [&](size_t i) {
             part[i].resize(b[i + 1] - b[i], comp);
-            ok(plsb_scores(e.ctx[i], Rr.data(), Rr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new), b[i + 1] - b[i],
-                           part[i].data()),
-               "plsb_scores");
+            return plsb_scores(e.ctx[i], Rr.data(), Rr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new), b[i + 1] - b[i],
+                               part[i].data());
         });
         for (size_t i = 0; i + 1 < b.size(); ++i) S.middleRows(b[i], b[i + 1] - b[i]) = part[i];
     }
@@ -177,11 +176,10 @@ const Mat2D Model::fitted_values(const Mat2D &X_new, const size_t comp) const {
     if (comp > 0) {
         const std::vector<int64_t> b = row_shards(e, X_new.rows());
         std::vector<Mat2D> part(b.size() - 1);
-        over_shards(e, b, [&](size_t i) {
+        over_shards(e, b, "plsb_fitted", [&](size_t i) {
             part[i].resize(b[i + 1] - b[i], Qr.rows());
-            ok(plsb_fitted(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i],
-                           ld(X_new), b[i + 1] - b[i], nullptr, 1, part[i].data()),
-               "plsb_fitted");
+            return plsb_fitted(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i],
+                               ld(X_new), b[i + 1] - b[i], nullptr, 1, part[i].data());
         });
         for (size_t i = 0; i + 1 < b.size(); ++i) F.middleRows(b[i], b[i + 1] - b[i]) = part[i];
     }
@@ -196,11 +194,10 @@ const Mat2D Model::residuals(const Mat2D &X_new, const Mat2D &Y_new, const size_
     Mat2D E(X_new.rows(), Qr.rows());
     const std::vector<int64_t> b = row_shards(e, X_new.rows());
     std::vector<Mat2D> part(b.size() - 1);
-    over_shards(e, b, [&](size_t i) {
+    over_shards(e, b, "plsb_fitted(residuals)", [&](size_t i) {
         part[i].resize(b[i + 1] - b[i], Qr.rows());
-        ok(plsb_fitted(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new),
-                       b[i + 1] - b[i], Y_new.data() + b[i], ld(Y_new), part[i].data()),
-           "plsb_fitted(residuals)");
+        return plsb_fitted(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new),
+                           b[i + 1] - b[i], Y_new.data() + b[i], ld(Y_new), part[i].data());
     });
     for (size_t i = 0; i + 1 < b.size(); ++i) E.middleRows(b[i], b[i + 1] - b[i]) = part[i];
     return E;
@@ -213,10 +210,9 @@ const Row Model::SSE(const Mat2D &X_new, const Mat2D &Y_new, const size_t comp) 
     const Mat2D Rr = R.real(), Qr = Q.real();
     const std::vector<int64_t> b = row_shards(e, X_new.rows());
     std::vector<Row> part(b.size() - 1, Row::Zero(Qr.rows()));
-    over_shards(e, b, [&](size_t i) {
-        ok(plsb_sse(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new),
-                    b[i + 1] - b[i], Y_new.data() + b[i], ld(Y_new), part[i].data()),
-           "plsb_sse");
+    over_shards(e, b, "plsb_sse", [&](size_t i) {
+        return plsb_sse(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)comp, X_new.data() + b[i], ld(X_new),
+                        b[i + 1] - b[i], Y_new.data() + b[i], ld(Y_new), part[i].data());
     });
     Row sse = part[0];
     for (size_t i = 1; i < part.size(); ++i) sse += part[i];   // shard order: deterministic
@@ -234,21 +230,24 @@ Residual Model::cv_on_device(const std::vector<int64_t> &test_idx, size_t nfolds
                              const char *label) const {
     Engine &e = Engine::get();
     std::lock_guard<std::recursive_mutex> lk(e.mu);
-    const int64_t M = _Y.cols(), rows = (int64_t)(nfolds * test_size);
+    if (!mirror) detail::die(label, PLSB_ERR_ARG, "the model holds no training data");
+    DeviceMirror &mir = *mirror;
+    const int64_t M = mir.M, rows = (int64_t)(nfolds * test_size);
     const int meth = method == KERNEL_TYPE2 ? PLSB_KERNEL_TYPE2 : PLSB_KERNEL_TYPE1;
     std::vector<double> E((size_t)(M * (int64_t)A * rows));
     const size_t ndev = std::min(e.ndev(), std::max<size_t>(nfolds, 1));
-    DeviceMirror &mir = *mirror;
-    if (mir.full.size() < e.ndev()) mir.full.resize(e.ndev(), nullptr);
-    auto work = [&](size_t i) {
-        if (i >= ndev) return;
+    mir.prepare();
+    auto work = [&](size_t i) -> int {
+        if (i >= ndev) return PLSB_OK;
         const int64_t f0 = (int64_t)(i * nfolds / ndev), f1 = (int64_t)((i + 1) * nfolds / ndev);
-        plsb_dataset_t ds = mir.full_on(i, _X.data(), ld(_X), _Y.data(), ld(_Y));
-        ok(plsb_cv_folds(ds, (int64_t)A, meth, (int64_t)nfolds, (int64_t)test_size, test_idx.data(), f0, f1 - f0, E.data()),
-           "plsb_cv_folds");
+        int rc = mir.ensure_full(i);   // replica on this GPU: device to device from the copy the fit left behind
+        if (rc == PLSB_OK)
+            rc = plsb_cv_folds(mir.full[i], (int64_t)A, meth, (int64_t)nfolds, (int64_t)test_size, test_idx.data(), f0, f1 - f0,
+                               E.data());
+        return rc;
     };
-    if (ndev == 1) work(0);
-    else e.parallel(work);
+    if (ndev == 1) ok(work(0), "plsb_cv_folds");
+    else e.parallel(work, "plsb_cv_folds");
     std::vector<Mat2D> Ev((size_t)M);
     for (int64_t m = 0; m < M; ++m)
         Ev[(size_t)m] = Eigen::Map<const Mat2D>(E.data() + (size_t)(m * (int64_t)A * rows), rows, (Eigen::Index)A);
@@ -256,14 +255,14 @@ Residual Model::cv_on_device(const std::vector<int64_t> &test_idx, size_t nfolds
 }
 
 Residual Model::cv_LOO() const {
-    const size_t N = _X.rows();
+    const size_t N = mirror ? (size_t)mirror->N : 0;
     std::vector<int64_t> idx(N);
     std::iota(idx.begin(), idx.end(), int64_t(0));
     return cv_on_device(idx, N, 1, "LOO");
 }
 
 Residual Model::cv_LSO(const float_type test_fraction, const size_t num_trials, std::mt19937 &rng) const {
-    const size_t N = _X.rows();
+    const size_t N = mirror ? (size_t)mirror->N : 0;
     const size_t test_size = static_cast<size_t>(test_fraction * N + 0.5);
     const size_t train_size = N - test_size;
     assert((test_size != 0) and (train_size != 0));
@@ -280,7 +279,7 @@ Residual Model::cv_LSO(const float_type test_fraction, const size_t num_trials, 
 }
 
 Residual Model::cv_NEW_DATA(const Mat2D &X_new, const Mat2D &Y_new) const {
-    assert((X_new.cols() == _X.cols()) and (Y_new.cols() == _Y.cols()));
+    assert((X_new.cols() == R.rows()) and (Y_new.cols() == Q.rows()));
     Engine &e = Engine::get();
     std::lock_guard<std::recursive_mutex> lk(e.mu);
     const Mat2D Rr = R.real(), Qr = Q.real();
@@ -292,14 +291,15 @@ Residual Model::cv_NEW_DATA(const Mat2D &X_new, const Mat2D &Y_new) const {
                                   Y_new.data(), ld(Y_new), E.data()),
            "plsb_predict_residuals");
     } else {
-        over_shards(e, b, [&](size_t i) {
+        over_shards(e, b, "plsb_predict_residuals", [&](size_t i) {
             const int64_t ri = b[i + 1] - b[i];
             std::vector<double> Ei((size_t)(M * (int64_t)A * ri));
-            ok(plsb_predict_residuals(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), M, (int64_t)A, X_new.data() + b[i],
-                                      ld(X_new), ri, Y_new.data() + b[i], ld(Y_new), Ei.data()),
-               "plsb_predict_residuals");
+            const int rc = plsb_predict_residuals(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), M, (int64_t)A, X_new.data() + b[i],
+                                                  ld(X_new), ri, Y_new.data() + b[i], ld(Y_new), Ei.data());
+            if (rc != PLSB_OK) return rc;
             for (int64_t mc = 0; mc < M * (int64_t)A; ++mc)   // column (m, c) of the block: rows [b[i], b[i+1])
                 std::copy(Ei.begin() + mc * ri, Ei.begin() + (mc + 1) * ri, E.begin() + mc * rows + b[i]);
+            return (int)PLSB_OK;
         });
     }
     std::vector<Mat2D> Ev((size_t)M);
@@ -312,18 +312,17 @@ Residual Model::cv_NEW_DATA(const Mat2D &X_new, const Mat2D &Y_new) const {
 void Model::print_explained_variance(const Mat2D &X, const Mat2D &Y, std::ostream &os) const {
     // one pass over X gives the SSE of every component count (the reference makes 2A passes)
     Engine &e = Engine::get();
-    Mat2D sse(_Y.cols() ? _Y.cols() : Y.cols(), A);
+    Mat2D sse(Y.cols(), A);
     {
         std::lock_guard<std::recursive_mutex> lk(e.mu);
         const Mat2D Rr = R.real(), Qr = Q.real();
         sse.setZero(Qr.rows(), A);
         const std::vector<int64_t> b = row_shards(e, X.rows());
         std::vector<Mat2D> part(b.size() - 1);
-        over_shards(e, b, [&](size_t i) {
+        over_shards(e, b, "plsb_sse_prefixes", [&](size_t i) {
             part[i].resize(Qr.rows(), A);
-            ok(plsb_sse_prefixes(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)A, X.data() + b[i], ld(X),
-                                 b[i + 1] - b[i], Y.data() + b[i], ld(Y), part[i].data()),
-               "plsb_sse_prefixes");
+            return plsb_sse_prefixes(e.ctx[i], Rr.data(), Qr.data(), Rr.rows(), Qr.rows(), (int64_t)A, X.data() + b[i], ld(X),
+                                     b[i + 1] - b[i], Y.data() + b[i], ld(Y), part[i].data());
         });
         for (const Mat2D &p : part) sse += p;
     }

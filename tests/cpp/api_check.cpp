@@ -61,6 +61,13 @@ int main(int argc, char **argv) {
     }
     dump(dir, "sse", sse);
     dump(dir, "ev", ev);
+    if (getenv("PLSB_TEST_RECONFIGURE")) {
+        // reconfigure the engine between the fit and the validation: the model's device copy of its training data was
+        // made on contexts the engine now lets go of, and must follow the model to the new ones
+        PLS::set_devices(PLS::devices());
+        Model other(X.topRows(X.rows() / 2), Y.topRows(X.rows() / 2), method, A);   // new contexts in use
+        (void)other;
+    }
     dump_residual(dir, "loo", m.cv_LOO());
     if (trials > 0) {
         std::mt19937 rng;

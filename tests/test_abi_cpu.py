@@ -98,10 +98,10 @@ def test_bench_reference_arm_prints_the_contract_line():
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1",
-                          "--cpu-sample", "5000"], capture_output=True, text=True, timeout=300, check=True).stdout
+                          "--ref-rows", "5000"], capture_output=True, text=True, timeout=300, check=True).stdout
     line = json.loads(out.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["metric"] == "pls_fits_per_sec" and line["unit"] == "fits/s"
     assert line["value"] > 0 and line["higher_is_better"] is True and line["dtype"] == "f64"
     assert line["cpu_baseline"]["kind"] in ("reference", "port") and line["cpu_baseline"]["cores"] == 1
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
-    assert "workload" in line["config"]
+    assert "workload" in line["config"] and line["config"]["sample_rows"] == 5000

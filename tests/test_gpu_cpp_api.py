@@ -104,6 +104,18 @@ def test_cpp_model_api_matches_reference(tmp_path, name, A, method, trials):
     assert relerr(d["refit_coef_A"], g[pre + "coef_A"]) <= RTOL
 
 
+@pytest.mark.skipif(not os.path.exists(API_CHECK), reason="tests/cpp/api_check not built (needs Eigen headers)")
+def test_cpp_model_survives_set_devices(tmp_path):
+    """PLS::set_devices between the constructor's fit and cv_LOO / cv_LSO: the engine lets go of the contexts the model's
+    device copy lives on (they are reference-counted by their data sets) and the copy is carried over to the new ones."""
+    g = load_golden("c2_nir_octane")
+    d = run_api_check(tmp_path, g["X_raw"], g["Y_raw"], 10, 0, 0.3, 600, zscore=True, env={"PLSB_TEST_RECONFIGURE": "1"})
+    assert relerr(stacked(d, "loo", 1), g["loo"]) <= RTOL
+    assert np.array_equal(d["loo_opt"].ravel().astype(int), g["loo_opt"].astype(int))
+    assert relerr(d["lso_ress"], g["lso_ress"]) <= RTOL
+    assert relerr(d["coef_A"], g["coef_A"]) <= RTOL
+
+
 NUM = re.compile(r"[-+]?(?:\d+\.?\d*|\.\d+)(?:[eE][-+]?\d+)?")
 
 
