@@ -483,14 +483,33 @@ def run_ours(args):
         te = np.arange(n5, dtype=np.int64).reshape(-1, 1)
         f0, f1 = sharding.fold_shard(n5, rank, world)
         E = np.zeros((m5, a5, n5))
-        ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=min(4096, f1 - f0), out=E)   # warm-up: one full wave (same buffers as the timed call)
-        ctx.profile(True); ctx.profile_reset()
+        ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)   # warm-up: the whole call (buffers, both lanes)
+        # (1) the timed call: two lanes in flight, no event between kernels
+        ctx.profile(False)
         barrier()
         t0 = time.perf_counter()
         ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)              # includes D2H of the residual block
         barrier()
         cv_s = time.perf_counter() - t0
-        gemm_ms, ngemm = ctx.profile_get("cv_gemm"); fold_ms, _ = ctx.profile_get("cv_fold"); xtx_ms, _ = ctx.profile_get("xtx")
+        # (2) the same call with an event pair around every kernel, lanes kept: kernel times INSIDE the overlap
+        ctx.profile(3); ctx.profile_reset()
+        t1 = time.perf_counter()
+        ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)
+        barrier()
+        cv_instr_s = time.perf_counter() - t1
+        gemm_ov, ngemm = ctx.profile_get("cv_gemm"); fold_ov, _ = ctx.profile_get("cv_fold"); xtx_ms, _ = ctx.profile_get("xtx")
+        # (3) the same kernels and buffers one after the other (PLSB_CV_SERIAL): each kernel alone on the GPU — the
+        # product kernel's FP64 tensor roofline, the fold kernels' HBM time
+        ctx.profile_reset()
+        os.environ["PLSB_CV_SERIAL"] = "1"
+        try:
+            t2 = time.perf_counter()
+            ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)
+            barrier()
+            cv_serial_s = time.perf_counter() - t2
+        finally:
+            del os.environ["PLSB_CV_SERIAL"]
+        gemm_ms, _ = ctx.profile_get("cv_gemm"); fold_ms, _ = ctx.profile_get("cv_fold")
         ctx.profile(False)
         if dist is not None:
             t = torch.tensor([cv_s], device="cuda", dtype=torch.float64)
@@ -510,11 +529,59 @@ def run_ours(args):
         gemm_tf = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else None
         cv = {"workload": "C5: synthetic X 20000x4096, Y x4, FP64, 64 components, full LOO-CV (20000 fits), folds sharded",
               "fits_per_s": n5 / cv_s, "seconds": cv_s, "folds": n5, "folds_this_rank": f1 - f0,
-              "kernels_ms_rank0": {"dmma_gemm": gemm_ms, "fold_kernels": fold_ms, "xtx": xtx_ms},
-              "gemm_roofline": {"bound": "tensor", "achieved": gemm_tf, "peak": fp64_peak, "unit": "TFLOP/s",
-                                "frac": (gemm_tf / fp64_peak) if (gemm_tf and fp64_peak) else None,
+              "schedule": "two lanes: the persistent DMMA product of one wave under the HBM-bound fold kernel of the other",
+              "kernels_ms_rank0": {"alone": {"dmma_gemm": gemm_ms, "fold_kernels": fold_ms, "call_s": cv_serial_s},
+                                   "overlapped": {"dmma_gemm": gemm_ov, "fold_kernels": fold_ov, "call_s": cv_instr_s},
+                                   "xtx": xtx_ms},
+              "gemm_roofline": {"bound": "tensor", "kernel": "cv_gemm_kernel, timed alone", "achieved": gemm_tf, "peak": fp64_peak,
+                                "unit": "TFLOP/s", "frac": (gemm_tf / fp64_peak) if (gemm_tf and fp64_peak) else None,
                                 "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul, measured in this run (calibration only)"}}
         ds5.close()
+
+    # ---- north_star's target sentence: LOO-CV on the 1M x 2048 matrix itself (pls.cpp:469-491 at N = 10^6): one million
+    # fits of A = 32 components, folds sharded over the ranks, every rank holding the whole matrix; X'X / X'Y built once
+    # (each rank reads its row slice, partial matrices all-reduced) and PRESS reduced on the device (the residual block,
+    # M*A*N*8 = 2 GB, never leaves HBM) -----
+    loo_c4 = None
+    if not args.no_cv and not args.no_loo_c4:
+        try:
+            ctx.trim()
+            ds4 = _capi.Dataset(ctx, synth=(C4["seed"], 0, N, K, M, C4["L"]))
+            te4 = np.arange(N, dtype=np.int64).reshape(-1, 1)
+            g0, g1 = sharding.fold_shard(N, rank, world)
+            ds4.cv_press(A, 0, te4, fold0=g0, nfolds_local=min(9472, g1 - g0))      # warm-up: one round of two waves
+            ctx.profile(3); ctx.profile_reset()
+            barrier()
+            t0 = time.perf_counter()
+            ds4.build_gram(across_ranks=world > 1)
+            barrier()
+            gram_s = time.perf_counter() - t0
+            xtx4_ms, _ = ctx.profile_get("xtx"); xty4_ms, _ = ctx.profile_get("pass_xty")
+            ctx.profile(False)
+            barrier()
+            t1 = time.perf_counter()
+            press = ds4.cv_press(A, 0, te4, fold0=g0, nfolds_local=g1 - g0)
+            barrier()
+            loo_s = time.perf_counter() - t1
+            if dist is not None:
+                t = torch.tensor([gram_s, loo_s], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                gram_s, loo_s = t.tolist()
+                pt = torch.tensor(np.ascontiguousarray(press), device="cuda", dtype=torch.float64)
+                dist.all_reduce(pt, op=dist.ReduceOp.SUM)
+                press = pt.cpu().numpy()
+            rows4 = (N // world) if world > 1 else N
+            loo_c4 = {"workload": "cv_LOO on the C4 matrix: 1,000,000 folds of 1M x 2048, Y x8, 32 components, folds sharded, PRESS on device",
+                      "fits_per_s": N / (gram_s + loo_s), "seconds": gram_s + loo_s, "folds": N, "folds_this_rank": g1 - g0,
+                      "cross_products": {"seconds": gram_s, "xtx_ms_rank0": xtx4_ms, "xty_ms_rank0": xty4_ms,
+                                         "rows_read_per_rank": rows4,
+                                         "xty_pass_GBps_rank0": 8.0 * rows4 * (K + M) / (xty4_ms * 1e-3) / 1e9 if xty4_ms > 0 else None,
+                                         "xtx_tflops_issued_rank0": float(rows4) * K * (K + 128) / (xtx4_ms * 1e-3) / 1e12 if xtx4_ms > 0 else None},
+                      "folds_seconds": loo_s, "gemm_tflops_if_alone": 2.0 * K * K * A * (g1 - g0) / loo_s / 1e12,
+                      "mse_last_component": [float(v) for v in (press[:, A - 1] / N)]}
+            ds4.close()
+        except Exception as e:
+            loo_c4 = {"error": repr(e)}
 
     # ---- configs 2 and 3: small-data CV (60 x ~400 spectra), one CTA per fold, all folds of a call in one wave -----
     cv_small = None
@@ -570,7 +637,7 @@ def run_ours(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "parallelism": f"rows sharded over {world} rank(s)",
                            "l2": "inputs (16.4 GB of X per fit pass) are larger than L2; no flush needed"},
-                "roofline": roofline, "parity": parity, "exchange": comm["exchange"], "cpu_baseline": cpu, "e2e": e2e, "e2e_cpp": e2e_cpp, "cv": cv, "cv_small": cv_small, "xtx_c4": xtx, "gpu_launches": int(launches), "clocks": clocks,
+                "roofline": roofline, "parity": parity, "exchange": comm["exchange"], "cpu_baseline": cpu, "e2e": e2e, "e2e_cpp": e2e_cpp, "cv": cv, "loo_c4": loo_c4, "cv_small": cv_small, "xtx_c4": xtx, "gpu_launches": int(launches), "clocks": clocks,
                 "device_ms_per_step": dev_timed_ms / max(n_timed, 1),
                 "instrumented": {"ms_per_step": instr_ms, "device_ms_per_fit": dev_ms / max(nfit, 1),
                                  "what": "the same K fits repeated with a CUDA event pair around every launch: source of the per-kernel times"}}
@@ -592,6 +659,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-cv", action="store_true")
     ap.add_argument("--no-xtx", action="store_true")
+    ap.add_argument("--no-loo-c4", action="store_true", help="skip the 1,000,000-fold LOO on the C4 matrix (~10 s on one GPU)")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--ref-rows", type=int, default=C4["N"],
                     help="reference arm: rows of the C4 matrix its timed fit runs on (default: all 1,000,000; fewer = a "

@@ -103,6 +103,10 @@ int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, dou
  * (bench.py's device-resident figure), uses. */
 int plsb_fit_resident(plsb_dataset_t ds, int64_t A, int method, plsb_model_t *model);
 int plsb_model_download(plsb_model_t model, double *W, double *P, double *R, double *Q, double *T);
+/* The N x A scores alone (column-major).  as_complex != 0: T receives N*A (re, im) pairs with im = 0 — the reference's
+ * Model::T is complex-typed (pls.h:251-254, Mat2Dc), so the drop-in fills its member straight from the transfer's
+ * staging buffers instead of widening a second host copy. */
+int plsb_model_download_scores(plsb_model_t model, double *T, int as_complex);
 int plsb_model_destroy(plsb_model_t model);
 /* One-shot form taking host matrices (upload + fit), the shape Model's constructor has (pls.cpp:340-353). */
 int plsb_fit_host(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K, const double *Y,
@@ -112,6 +116,12 @@ int plsb_fit_host(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64
 /* ---- cross products: XY = X'Y (pls.cpp:396), XX = X'X (pls.cpp:398, FP64 DMMA) -------------- */
 int plsb_xty(plsb_dataset_t ds, double *XY /* K x M col-major */);
 int plsb_xtx(plsb_dataset_t ds, double *XX /* K x K col-major, may be NULL: device only */);
+
+/* Build XX = X'X and XY = X'Y once and KEEP them on the data set (pls.cpp:396, 398; the matrices an upload from host
+ * memory accumulates under the transfer): plsb_cv_folds* and fits that follow start from them instead of rebuilding them
+ * per call.  across_ranks != 0 — a replicated data set on a context with a communicator, collective: rank g reads rows
+ * [g N/G, (g+1) N/G) only and the partial matrices are summed over the ranks. */
+int plsb_dataset_build_gram(plsb_dataset_t ds, int across_ranks);
 
 /* ---- prediction: scores / fitted_values / residuals / cv_NEW_DATA (pls.cpp:439-459, 494-510) -- */
 /* S = Xn * R[:, :comp]   (Nn x comp) */
@@ -194,7 +204,9 @@ int plsb_lso_folds(int64_t N, double test_fraction, int64_t num_trials, uint32_t
 #define PLSB_PROF_SCORES 9      /* DMMA scores S = X R */
 #define PLSB_PROF_NSLOTS 10
 /* on: 0 off; 1 a CUDA event pair around every launch group; 2 only around whole fits (device time of a fit without
- * an event between its kernels, which would switch off their programmatic dependent launch) */
+ * an event between its kernels, which would switch off their programmatic dependent launch); 3 like 1, but the
+ * two-lane cross-validation engine keeps both lanes in flight and its kernels are timed inside the overlap (1 runs it
+ * as one lane, so that kernel times add up to the call) */
 int plsb_profile_enable(plsb_ctx_t ctx, int on);
 int plsb_profile_reset(plsb_ctx_t ctx);
 /* total milliseconds and launch count accumulated in a slot since the last reset */

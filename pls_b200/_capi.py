@@ -21,8 +21,8 @@ SYMBOLS = [
     "plsb_last_error", "plsb_version", "plsb_device_count", "plsb_ctx_create", "plsb_ctx_destroy", "plsb_ctx_sync", "plsb_ctx_trim",
     "plsb_comm_unique_id", "plsb_comm_init", "plsb_comm_allreduce_test", "plsb_comm_info",
     "plsb_dataset_create", "plsb_dataset_create_device", "plsb_dataset_create_synth", "plsb_dataset_destroy",
-    "plsb_dataset_shape", "plsb_dataset_concat", "plsb_dataset_download", "plsb_dataset_set_sharded",
-    "plsb_fit", "plsb_fit_resident", "plsb_model_download", "plsb_model_destroy", "plsb_fit_host", "plsb_xty", "plsb_xtx",
+    "plsb_dataset_shape", "plsb_dataset_concat", "plsb_dataset_download", "plsb_dataset_set_sharded", "plsb_dataset_build_gram",
+    "plsb_fit", "plsb_fit_resident", "plsb_model_download", "plsb_model_download_scores", "plsb_model_destroy", "plsb_fit_host", "plsb_xty", "plsb_xtx",
     "plsb_scores", "plsb_fitted", "plsb_predict_residuals", "plsb_coefficients", "plsb_sse_prefixes", "plsb_sse",
     "plsb_cv_folds", "plsb_cv_folds_press", "plsb_colstats", "plsb_colwise_z_scores", "plsb_dataset_zscore",
     "plsb_normalcdf", "plsb_wilcoxon", "plsb_validation", "plsb_optimal_num_components", "plsb_lso_folds",
@@ -114,8 +114,9 @@ class Context:
 
     # -- profiling -----------------------------------------------------------------------------
     def profile(self, on=True):
-        """on: False/0 off, True/1 events around every launch group, 2 only around whole fits"""
-        check(lib().plsb_profile_enable(self.h, C.c_int(2 if on == 2 else (1 if on else 0))))
+        """on: False/0 off, True/1 events around every launch group, 2 only around whole fits, 3 like 1 with the CV
+        engine's two lanes kept (kernels timed inside the overlap)"""
+        check(lib().plsb_profile_enable(self.h, C.c_int(int(on) if on in (2, 3) else (1 if on else 0))))
 
     def profile_reset(self):
         check(lib().plsb_profile_reset(self.h))
@@ -224,6 +225,10 @@ class Dataset:
         G = np.zeros((self.K, self.K), order="F") if download else None
         check(lib().plsb_xtx(self.h, P(G)))
         return G
+
+    def build_gram(self, across_ranks=False):
+        """X'X and X'Y built once and kept on the data set (collective when across_ranks: every rank reads its row slice)."""
+        check(lib().plsb_dataset_build_gram(self.h, C.c_int(1 if across_ranks else 0)))
 
     def cv_folds(self, A, method, test_idx, fold0=0, nfolds_local=None, out=None):
         """test_idx: (nfolds_total, test_size) int64 rows left out per fold; folds [fold0, fold0+nfolds_local)

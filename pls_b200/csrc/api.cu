@@ -118,7 +118,7 @@ int ensure_part(plsb_ctx *c, size_t bytes) {
     return PLSB_OK;
 }
 
-ProfScope::ProfScope(plsb_ctx *ctx, int slot) : c(ctx) {
+ProfScope::ProfScope(plsb_ctx *ctx, int slot, cudaStream_t stream) : c(ctx), st(stream ? stream : ctx->stream) {
     if (slot < 0 || !c->prof || (c->prof == 2 && slot != PLSB_PROF_FIT_TOTAL)) return;
     plsb_ctx::Pending p;
     p.slot = slot;
@@ -126,12 +126,12 @@ ProfScope::ProfScope(plsb_ctx *ctx, int slot) : c(ctx) {
         if (!c->pool.empty()) { *e = c->pool.back(); c->pool.pop_back(); }
         else if (cudaEventCreate(e) != cudaSuccess) return;
     }
-    cudaEventRecord(p.a, c->stream);
+    cudaEventRecord(p.a, st);
     c->pending.push_back(p);
     idx = (int)c->pending.size() - 1;
 }
 ProfScope::~ProfScope() {
-    if (idx >= 0) cudaEventRecord(c->pending[idx].b, c->stream);
+    if (idx >= 0) cudaEventRecord(c->pending[idx].b, st);
 }
 
 static int prof_drain(plsb_ctx *c) {
@@ -282,7 +282,7 @@ int plsb_comm_info(plsb_ctx_t c, int *rank, int *nranks, int *peer_exchange) {
 int plsb_profile_enable(plsb_ctx_t c, int on) {
     PLSB_ARG(c, "ctx is null");
     PLSB_TRY(prof_drain(c));
-    c->prof = on == 2 ? 2 : (on != 0 ? 1 : 0);
+    c->prof = (on == 2 || on == 3) ? on : (on != 0 ? 1 : 0);
     return PLSB_OK;
 }
 int plsb_profile_reset(plsb_ctx_t c) {

@@ -13,10 +13,12 @@
 // e_a = e_{a-1} - u q_a' : no separate prediction pass.
 // Components are extracted up to A only (the reference extracts K per fold, pls.cpp:477/531; its first A
 // are bit-identical).
+#include <type_traits>
 #include <vector>
 
 #include "internal.h"
 #include "step_core.cuh"
+#include "step_wide.cuh"
 
 namespace plsb {
 
@@ -30,11 +32,16 @@ struct CvArgs {
     int K, ldk, ldm, M, A, ts;
     int f0;                    // first local fold of this wave
     int a;                     // component whose GEMM just finished (-1: initialise)
+    double *Rt;                // two-lane engine: the next r also goes here, in the tiled layout of cv_gemm.cu (or null)
+    int nkt;
+    double *wide;              // M > 32: per-fold scratch of wide_scratch_doubles(M) doubles (step_wide.cuh), else null
 };
 
+// WIDE: M > 32 responses — the M-sized objects live in a per-fold global scratch (step_wide.cuh)
+template <bool WIDE>
 __global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
-    __shared__ StepSmem<CV_NT> sh;
-    __shared__ double qdump[PLSB_MAX_M];
+    __shared__ typename std::conditional<WIDE, WideSmem<CV_NT>, StepSmem<CV_NT>>::type sh;
+    __shared__ double qdump[WIDE ? 1 : PLSB_MAX_M];
     const int tid = threadIdx.x;
     const int f = blockIdx.x;
     const int64_t gf = (int64_t)v.f0 + f;
@@ -43,6 +50,7 @@ __global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
     double *Sf = v.S + (size_t)f * M * ldk;
     double *Pf = v.P + (size_t)f * v.A * ldk;
     double *Rf = v.R + (size_t)f * v.A * ldk;
+    double *wide = WIDE ? v.wide + (size_t)f * wide_scratch_doubles(M) : nullptr;
 
     if (v.a < 0) {
         // S_f = S0 - X_H' Y_H
@@ -73,21 +81,34 @@ __global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
         }
         double acc = 0.0;
         for (int k = tid; k < K; k += CV_NT) acc = fma(r[k], g[k], acc);
-        const double tt = block_sum<CV_NT>(acc, sh);
-        finish_component<CV_NT>(K, ldk, M, Sf, g, tt, r, Pf + (size_t)v.a * ldk, qdump, sh);
+        const double *qv;
+        if constexpr (WIDE) {
+            const double tt = wide_block_sum<CV_NT>(acc, sh);
+            qv = wide + 2 * (size_t)M * M;
+            finish_component_wide<CV_NT>(K, ldk, M, Sf, g, tt, r, Pf + (size_t)v.a * ldk, wide + 2 * (size_t)M * M, wide);
+        } else {
+            const double tt = block_sum<CV_NT>(acc, sh);
+            qv = sh.q;
+            finish_component<CV_NT>(K, ldk, M, Sf, g, tt, r, Pf + (size_t)v.a * ldk, qdump, sh);
+        }
         // residuals of the held-out rows with a+1 components: e_a = e_{a-1} - u q_a'
         for (int e = tid; e < v.ts * M; e += CV_NT) {
             const int i = e / M, m = e % M;
             const int64_t row = gf * v.ts + i;
             const double prev = (v.a == 0) ? v.Y[h[i] * (int64_t)v.ldm + m]
                                            : v.E[((size_t)m * v.A + (v.a - 1)) * v.rows_local + row];
-            v.E[((size_t)m * v.A + v.a) * v.rows_local + row] = prev - U[i] * sh.q[m];
+            v.E[((size_t)m * v.A + v.a) * v.rows_local + row] = prev - U[i] * qv[m];
         }
         __syncthreads();
     }
     const int an = v.a + 1;
     if (an >= v.A) return;
-    next_weights<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, sh);
+    if constexpr (WIDE) next_weights_wide<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, wide, sh);
+    else next_weights<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, sh);
+    if (v.Rt) {   // (every thread re-reads the elements it wrote itself: same k -> thread mapping as next_weights)
+        const double *rn = Rf + (size_t)an * ldk;
+        for (int k = tid; k < K; k += CV_NT) v.Rt[cv_gemm_rt_index(v.nkt, f, k)] = rn[k];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -137,7 +158,7 @@ struct FusedSmem {
     double q[MM];
     double c[256];
     double gram[MM * MM];
-    double V[MM * MM];
+    double B[2 * 64];        // work arrays of the squaring eigen solver (8 x 8 padded, two buffers)
 };
 
 template <int MM>
@@ -261,7 +282,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
                 }
         }
         __syncthreads();
-        if (tid < 32) jacobi_dominant_warp(sh.gram, sh.V, M, qe);
+        if (tid < 32) dominant_eigvec_warp<8>(sh.gram, sh.B, sh.B + 64, M, qe);
         __syncthreads();
     }
     double wv[CV_KPT];
@@ -311,7 +332,10 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
 #pragma unroll
     for (int j = 0; j < CV_KPT; ++j) {
         const int k = tid + CV_FNT * j;
-        if (k < K) rn[k] = wv[j];
+        if (k < K) {
+            rn[k] = wv[j];
+            if (v.Rt) v.Rt[cv_gemm_rt_index(v.nkt, f, k)] = wv[j];
+        }
     }
     for (int k = K + tid; k < ldk; k += CV_FNT) rn[k] = 0.0;
 }
@@ -397,10 +421,6 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     PLSB_ARG(method == PLSB_KERNEL_TYPE1 || method == PLSB_KERNEL_TYPE2, "unknown method %d", method);
     PLSB_ARG(test_size >= 1 && test_size < ds->N, "test_size %lld must be in [1, N)", (long long)test_size);
     PLSB_ARG(fold0 >= 0 && nfolds_local >= 0 && fold0 + nfolds_local <= nfolds_total, "bad fold range");
-    if (ds->M > PLSB_MAX_M) {
-        set_error("M=%lld responses exceed the in-kernel eigen solver limit (%d)", (long long)ds->M, PLSB_MAX_M);
-        return PLSB_ERR_UNSUPPORTED;
-    }
     PLSB_ARG(!ds->sharded, "cross-validation wants the full data set on every GPU (folds are sharded, not rows)");
     const int64_t K = ds->K, ldk = ds->ldk, M = ds->M, ts = test_size;
     if (nfolds_local == 0) {
@@ -414,7 +434,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         PLSB_ARG(tloc[i] >= 0 && tloc[i] < ds->N, "test index %lld out of range", (long long)tloc[i]);
     const int64_t rows_local = nfolds_local * ts, rows_total = nfolds_total * ts;
 
-    CvBuf G(c), S0(c), idx(c), Ed(c), S(c), P(c), R(c), w(c), Gr(c), U(c);
+    CvBuf G(c), S0(c), idx(c), Ed(c);
     PLSB_TRY(idx.alloc((size_t)rows_local * sizeof(int64_t)));
     PLSB_CUDA(cudaMemcpyAsync(idx.p, tloc, (size_t)rows_local * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
     PLSB_TRY(Ed.alloc((size_t)M * A * rows_local * 8));
@@ -451,54 +471,188 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         Gfull = G.d(); S0full = S0.d();
     }
 
+    // ---- waves and lanes ------------------------------------------------------------------------------------------
+    // The batched GEMM is FP64-tensor-bound and leaves HBM idle; the fold kernel is HBM-bound and leaves the tensor
+    // pipe idle.  With two LANES (two waves in flight, each with its own S/P/R/w/Gr/U buffers) the GEMM of one lane runs
+    // under the fold kernel of the other: all GEMMs go to one high-priority stream, all fold kernels to a low-priority
+    // one, chained per lane by events (fold(a) after GEMM(a), GEMM(a+1) after fold(a)):
+    //      gemm stream:  G0(0) | G1(0) | G0(1) | G1(1) | ...
+    //      fold stream:        | F0(0) | F1(0) | F0(1) | ...
+    // The product runs as a persistent kernel over pre-tiled operands (one CTA per SM, 8 warps x 168 registers, two bulk
+    // copies per stage: cv_gemm.cu), so the fold CTAs are placed in the quarter of each SM it leaves free.  One lane on the context's stream is kept for
+    // per-kernel profiling (profile mode 1), small calls and as the A/B reference (PLSB_CV_LANES=1).
+    int lanes = 2;
+    if (const char *e = getenv("PLSB_CV_LANES")) { const int l = atoi(e); if (l == 1 || l == 2) lanes = l; }
+    if (c->prof == 1 || nfolds_local < 512) lanes = 1;
     // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles.  At most 4736
     // folds = 37 column tiles of the batched GEMM: with K = 4096 (32 row tiles) that is 1184 CTAs = 8 full waves of
     // 148 SMs, with K = 2048 four.
     size_t free_b = 0;
     PLSB_TRY(dev_mem_available(c, &free_b));
-    const size_t per_fold = (size_t)(M + 2 * A + 2) * ldk * 8 + (size_t)ts * 8;
-    int64_t F = (int64_t)((double)free_b * 0.6 / (double)per_fold);
+    const size_t per_fold = (size_t)(M + 2 * A + 2) * ldk * 8 + (size_t)ts * 8 + (lanes == 2 ? (size_t)ldk * 9 + 64 : 0) +
+                            step_wide_scratch_bytes((int)M);
+    int64_t F = (int64_t)((double)free_b * 0.6 / (double)per_fold) / lanes;
     if (F > 4736) F = 4736;
     if (const char *e = getenv("PLSB_FOLD_BATCH")) { const int64_t v = atoll(e); if (v > 0 && v < F) F = v; }
-    if (F > nfolds_local) F = nfolds_local;
+    if (F < 1 && lanes == 2) { lanes = 1; F = (int64_t)((double)free_b * 0.6 / (double)per_fold); }
     PLSB_ARG(F >= 1, "not enough device memory for one fold");
-    PLSB_TRY(S.alloc((size_t)F * M * ldk * 8));
-    PLSB_TRY(P.alloc((size_t)F * A * ldk * 8));
-    PLSB_TRY(R.alloc((size_t)F * A * ldk * 8));
-    PLSB_TRY(w.alloc((size_t)F * ldk * 8));
-    PLSB_TRY(Gr.alloc((size_t)F * ldk * 8));
-    PLSB_TRY(U.alloc((size_t)F * ts * 8));
+    if (lanes == 2) {    // equal waves, an even number of them, whole GEMM column tiles (128 folds) except the last
+        const int64_t nw = 2 * ceil_div(nfolds_local, 2 * F);
+        const int64_t Fe = round_up(ceil_div(nfolds_local, nw), 128);
+        if (Fe < F) F = Fe;
+    }
+    if (F > nfolds_local) F = nfolds_local;
+
+    struct Lane { CvBuf S, P, R, w, Gr, U, Rt, wide; cudaEvent_t evG = nullptr, evF = nullptr; explicit Lane(plsb_ctx *c) : S(c), P(c), R(c), w(c), Gr(c), U(c), Rt(c), wide(c) {} };
+    Lane lane0(c), lane1(c);
+    Lane *ln[2] = {&lane0, &lane1};
+    for (int l = 0; l < lanes; ++l) {
+        PLSB_TRY(ln[l]->S.alloc((size_t)F * M * ldk * 8));
+        PLSB_TRY(ln[l]->P.alloc((size_t)F * A * ldk * 8));
+        PLSB_TRY(ln[l]->R.alloc((size_t)F * A * ldk * 8));
+        PLSB_TRY(ln[l]->w.alloc((size_t)F * ldk * 8));
+        PLSB_TRY(ln[l]->Gr.alloc((size_t)F * ldk * 8));
+        PLSB_TRY(ln[l]->U.alloc((size_t)F * ts * 8));
+        if (const size_t wb = step_wide_scratch_bytes((int)M)) PLSB_TRY(ln[l]->wide.alloc((size_t)F * wb));
+    }
+    CvBuf Gt(c);
+    const int nkt = (int)ceil_div(K, CVG_BK);
+    if (lanes == 2) {   // operands of the persistent product kernel in its tiled layouts (cv_gemm.cu); the padding stays zero
+        PLSB_TRY(Gt.alloc(cv_gemm_gt_doubles(K) * 8));
+        PLSB_TRY(launch_cv_gemm_tile_g(c, c->stream, Gfull, ldg, K, Gt.d()));
+        for (int l = 0; l < 2; ++l) {
+            const size_t nb = cv_gemm_rt_doubles(K, F) * 8;
+            PLSB_TRY(ln[l]->Rt.alloc(nb));
+            PLSB_CUDA(cudaMemsetAsync(ln[l]->Rt.p, 0, nb, c->stream));
+        }
+    }
 
     CvArgs v{};
-    v.X = ds->X; v.Y = ds->Y; v.S0 = S0full; v.test_idx = (const int64_t *)idx.p;
-    v.S = S.d(); v.P = P.d(); v.R = R.d(); v.w = w.d(); v.Gr = Gr.d(); v.U = U.d(); v.E = Ed.d();
+    v.X = ds->X; v.Y = ds->Y; v.S0 = S0full; v.test_idx = (const int64_t *)idx.p; v.E = Ed.d();
     v.rows_local = rows_local; v.K = (int)K; v.ldk = (int)ldk; v.ldm = (int)ds->ldm; v.M = (int)M; v.A = (int)A;
     v.ts = (int)ts;
     const char *v1 = getenv("PLSB_CV_V1");   // A/B switch: the phase-by-phase kernel for every launch
     const bool fused = K >= 1024 && K <= (int64_t)CV_KPT * CV_FNT && M <= 8 && ts <= 256 && !(v1 && *v1 == '1');
-    for (int64_t f0 = 0; f0 < nfolds_local; f0 += F) {
-        const int nf = (int)(nfolds_local - f0 < F ? nfolds_local - f0 : F);
-        v.f0 = (int)f0;
-        for (int a = -1; a < (int)A; ++a) {
-            v.a = a;
-            if (a >= 0)  // Gr[f][:] = (X'X) r_f for the whole wave: one DMMA GEMM
-                PLSB_TRY(launch_gemm_atb(c, Gfull, ldg, R.d() + (size_t)a * ldk, A * ldk, K, (int)K, nf, Gr.d(), ldk,
-                                         false, true, true, PLSB_PROF_CV_GEMM));
-            {
+    if (lanes == 2) {
+        // An SM runs with ONE shared-memory carve-out at a time: a kernel that prefers a different split of the 256 KB
+        // L1/shared array than the resident product kernel (which needs the maximum) is not placed next to it.  Ask for
+        // the same carve-out for the fold kernels, so that they can share the SMs.  (PLSB_CV_CARVEOUT=0: A/B)
+        const char *ce = getenv("PLSB_CV_CARVEOUT");
+        const int carve = (ce && *ce == '0') ? cudaSharedmemCarveoutDefault : cudaSharedmemCarveoutMaxShared;
+        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+    }
+    auto launch_fold = [&](cudaStream_t st, int a, int nf) -> int {
+        if (a >= 0 && fused) {
+            if (M == 1) cv_fold_fused_kernel<1><<<nf, CV_FNT, 0, st>>>(v);
+            else if (M == 2) cv_fold_fused_kernel<2><<<nf, CV_FNT, 0, st>>>(v);
+            else if (M <= 4) cv_fold_fused_kernel<4><<<nf, CV_FNT, 0, st>>>(v);
+            else cv_fold_fused_kernel<8><<<nf, CV_FNT, 0, st>>>(v);
+        } else if (M > PLSB_MAX_M) {
+            cv_fold_kernel<true><<<nf, CV_NT, 0, st>>>(v);
+        } else {
+            cv_fold_kernel<false><<<nf, CV_NT, 0, st>>>(v);
+        }
+        c->launches++;
+        PLSB_CUDA(cudaGetLastError());
+        return PLSB_OK;
+    };
+    auto bind = [&](Lane &L, int64_t f0) {
+        v.S = L.S.d(); v.P = L.P.d(); v.R = L.R.d(); v.w = L.w.d(); v.Gr = L.Gr.d(); v.U = L.U.d(); v.f0 = (int)f0;
+        v.Rt = L.Rt.d(); v.nkt = nkt; v.wide = L.wide.d();
+    };
+
+    if (lanes == 1) {
+        Lane &L = lane0;
+        for (int64_t f0 = 0; f0 < nfolds_local; f0 += F) {
+            const int nf = (int)(nfolds_local - f0 < F ? nfolds_local - f0 : F);
+            bind(L, f0);
+            for (int a = -1; a < (int)A; ++a) {
+                v.a = a;
+                if (a >= 0)  // Gr[f][:] = (X'X) r_f for the whole wave: one DMMA GEMM
+                    PLSB_TRY(launch_gemm_atb(c, Gfull, ldg, L.R.d() + (size_t)a * ldk, A * ldk, K, (int)K, nf, L.Gr.d(), ldk,
+                                             false, true, true, PLSB_PROF_CV_GEMM, false, nullptr, /*no_split=*/true));
                 ProfScope ps(c, PLSB_PROF_CV_FOLD);
-                if (a >= 0 && fused) {
-                    if (M == 1) cv_fold_fused_kernel<1><<<nf, CV_FNT, 0, c->stream>>>(v);
-                    else if (M == 2) cv_fold_fused_kernel<2><<<nf, CV_FNT, 0, c->stream>>>(v);
-                    else if (M <= 4) cv_fold_fused_kernel<4><<<nf, CV_FNT, 0, c->stream>>>(v);
-                    else cv_fold_fused_kernel<8><<<nf, CV_FNT, 0, c->stream>>>(v);
-                } else {
-                    cv_fold_kernel<<<nf, CV_NT, 0, c->stream>>>(v);
-                }
+                PLSB_TRY(launch_fold(c->stream, a, nf));
             }
-            c->launches++;
-            PLSB_CUDA(cudaGetLastError());
+        }
+        return finish();
+    }
+
+    // ---- two lanes ----------------------------------------------------------------------------------------------
+    struct Streams {
+        cudaStream_t g = nullptr, f = nullptr;
+        cudaEvent_t e0 = nullptr, e1 = nullptr;
+        bool own = true;
+        ~Streams() {
+            if (g && own) { cudaStreamSynchronize(g); cudaStreamDestroy(g); }
+            if (f && own) { cudaStreamSynchronize(f); cudaStreamDestroy(f); }
+            if (e0) cudaEventDestroy(e0);
+            if (e1) cudaEventDestroy(e1);
+        }
+    } sx;
+    struct EvGuard { Lane **ln; ~EvGuard() { for (int l = 0; l < 2; ++l) { if (ln[l]->evG) cudaEventDestroy(ln[l]->evG); if (ln[l]->evF) cudaEventDestroy(ln[l]->evF); } } } evguard{ln};
+    {
+        int lo = 0, hi = 0;
+        PLSB_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));   // lo = least, hi = greatest (numerically lower)
+        const char *pe = getenv("PLSB_CV_PRIO");
+        const bool prio = !(pe && *pe == '0');
+        const char *se = getenv("PLSB_CV_SERIAL");   // measurement aid: the same kernels and buffers, one after the other
+        if (se && *se == '1') {
+            sx.own = false; sx.g = sx.f = c->stream;
+        } else {
+            PLSB_CUDA(cudaStreamCreateWithPriority(&sx.g, cudaStreamNonBlocking, prio ? hi : 0));
+            PLSB_CUDA(cudaStreamCreateWithPriority(&sx.f, cudaStreamNonBlocking, prio ? lo : 0));
+        }
+        PLSB_CUDA(cudaEventCreateWithFlags(&sx.e0, cudaEventDisableTiming));
+        PLSB_CUDA(cudaEventCreateWithFlags(&sx.e1, cudaEventDisableTiming));
+        for (int l = 0; l < 2; ++l) {
+            PLSB_CUDA(cudaEventCreateWithFlags(&ln[l]->evG, cudaEventDisableTiming));
+            PLSB_CUDA(cudaEventCreateWithFlags(&ln[l]->evF, cudaEventDisableTiming));
         }
     }
+    // everything queued so far (allocations, index upload, the cross products) happens before the lanes start
+    PLSB_CUDA(cudaEventRecord(sx.e0, c->stream));
+    PLSB_CUDA(cudaStreamWaitEvent(sx.g, sx.e0, 0));
+    PLSB_CUDA(cudaStreamWaitEvent(sx.f, sx.e0, 0));
+    for (int64_t f0 = 0; f0 < nfolds_local; f0 += 2 * F) {
+        int nfl[2];
+        for (int l = 0; l < 2; ++l) {
+            const int64_t left = nfolds_local - (f0 + l * F);
+            nfl[l] = (int)(left < 0 ? 0 : (left < F ? left : F));
+        }
+        for (int a = -1; a < (int)A; ++a) {
+            v.a = a;
+            for (int l = 0; l < 2; ++l) {
+                if (nfl[l] == 0) continue;
+                Lane &L = *ln[l];
+                bind(L, f0 + l * F);
+                if (a >= 0) {
+                    PLSB_CUDA(cudaStreamWaitEvent(sx.g, L.evF, 0));            // r_a of this lane is ready
+                    {
+                        ProfScope ps(c, PLSB_PROF_CV_GEMM, sx.g);
+                        PLSB_TRY(launch_cv_gemm(c, sx.g, Gt.d(), L.Rt.d(), K, ldk, nfl[l], L.Gr.d()));
+                    }
+                    PLSB_CUDA(cudaEventRecord(L.evG, sx.g));
+                    PLSB_CUDA(cudaStreamWaitEvent(sx.f, L.evG, 0));
+                }
+                {
+                    ProfScope ps(c, PLSB_PROF_CV_FOLD, sx.f);
+                    PLSB_TRY(launch_fold(sx.f, a, nfl[l]));
+                }
+                PLSB_CUDA(cudaEventRecord(L.evF, sx.f));
+            }
+        }
+    }
+    // the context's stream continues (PRESS, D2H of the residual block, frees) once both streams have drained
+    PLSB_CUDA(cudaEventRecord(sx.e0, sx.g));
+    PLSB_CUDA(cudaEventRecord(sx.e1, sx.f));
+    PLSB_CUDA(cudaStreamWaitEvent(c->stream, sx.e0, 0));
+    PLSB_CUDA(cudaStreamWaitEvent(c->stream, sx.e1, 0));
     return finish();
 }
 

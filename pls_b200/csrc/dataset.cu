@@ -3,6 +3,7 @@
 // streaming passes want.
 #include <string.h>
 
+#include <chrono>
 #include <thread>
 
 #include "host_pool.h"
@@ -22,7 +23,7 @@ static bool host_is_pageable(const void *p) {
     return e != cudaSuccess || a.type == cudaMemoryTypeUnregistered;
 }
 
-static int hstage_ensure(plsb_ctx *c, size_t bytes) {
+static void hstage_pool(plsb_ctx *c) {
     plsb_ctx::HostStage &h = c->hstage;
     if (!h.pool) {
         int n = 0;
@@ -35,6 +36,52 @@ static int hstage_ensure(plsb_ctx *c, size_t bytes) {
         }
         h.pool = new HostPool(n);
     }
+}
+
+int download_staged(plsb_ctx *c, const double *dev, size_t n, double *host, bool as_complex) {
+    if (n == 0) return PLSB_OK;
+    plsb_ctx::HostStage &h = c->hstage;
+    hstage_pool(c);
+    const size_t chunk = (size_t)32 << 20;
+    if (!h.dbuf[0]) {
+        for (int i = 0; i < 2; ++i) {
+            PLSB_CUDA(cudaHostAlloc((void **)&h.dbuf[i], chunk, cudaHostAllocDefault));
+            PLSB_CUDA(cudaEventCreateWithFlags(&h.ddone[i], cudaEventDisableTiming));
+        }
+        h.dbytes = chunk;
+    }
+    PLSB_CUDA(cudaEventRecord(c->col_ev, c->stream));                 // the source is complete
+    PLSB_CUDA(cudaStreamWaitEvent(c->copy_stream, c->col_ev, 0));
+    const size_t per = chunk / 8, nch = (n + per - 1) / per;
+    auto move_out = [&](size_t i) {
+        const size_t off = i * per, cnt = n - off < per ? n - off : per;
+        const double *src = (const double *)h.dbuf[i & 1];
+        h.pool->run([&](int t, int nt) {
+            const size_t a = cnt / (size_t)nt * (size_t)t, b = (t + 1 == nt) ? cnt : cnt / (size_t)nt * (size_t)(t + 1);
+            if (!as_complex) memcpy(host + off + a, src + a, (b - a) * 8);
+            else {
+                double *d = host + 2 * (off + a);
+                for (size_t j = a; j < b; ++j) { *d++ = src[j]; *d++ = 0.0; }
+            }
+        });
+    };
+    for (size_t i = 0; i < nch; ++i) {
+        const size_t off = i * per, cnt = n - off < per ? n - off : per;
+        PLSB_CUDA(cudaMemcpyAsync(h.dbuf[i & 1], dev + off, cnt * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+        PLSB_CUDA(cudaEventRecord(h.ddone[i & 1], c->copy_stream));
+        if (i > 0) {
+            PLSB_CUDA(cudaEventSynchronize(h.ddone[(i - 1) & 1]));
+            move_out(i - 1);
+        }
+    }
+    PLSB_CUDA(cudaEventSynchronize(h.ddone[(nch - 1) & 1]));
+    move_out(nch - 1);
+    return PLSB_OK;
+}
+
+static int hstage_ensure(plsb_ctx *c, size_t bytes) {
+    plsb_ctx::HostStage &h = c->hstage;
+    hstage_pool(c);
     if (bytes <= h.bytes) return PLSB_OK;
     for (int i = 0; i < 3; ++i) {
         if (h.done[i]) cudaEventSynchronize(h.done[i]);
@@ -58,6 +105,10 @@ void hstage_release(plsb_ctx *c) {
     for (int i = 0; i < 3; ++i) {
         if (h.done[i]) cudaEventDestroy(h.done[i]);
         if (h.buf[i]) cudaFreeHost(h.buf[i]);
+    }
+    for (int i = 0; i < 2; ++i) {
+        if (h.ddone[i]) cudaEventDestroy(h.ddone[i]);
+        if (h.dbuf[i]) cudaFreeHost(h.dbuf[i]);
     }
     delete h.pool;
     h = plsb_ctx::HostStage();
@@ -95,9 +146,14 @@ static cudaError_t send_block(plsb_ctx *c, bool staged, int64_t i, double *buf, 
                                  cudaMemcpyHostToDevice, c->copy_stream);
     plsb_ctx::HostStage &h = c->hstage;
     const int hb = (int)(i % 3);
+    const auto t0 = std::chrono::steady_clock::now();
     cudaError_t e = cudaEventSynchronize(h.done[hb]);   // the copy that read this buffer three blocks ago
     if (e != cudaSuccess) return e;
+    const auto t1 = std::chrono::steady_clock::now();
     pack_segments(*h.pool, h.buf[hb], (const char *)src, (size_t)nr * 8, (size_t)lds * 8, (size_t)nseg);
+    h.wait_s += std::chrono::duration<double>(t1 - t0).count();
+    h.pack_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - t1).count();
+    h.pack_bytes += (double)nr * 8.0 * (double)nseg;
     e = cudaMemcpyAsync(buf, h.buf[hb], (size_t)nr * 8 * (size_t)nseg, cudaMemcpyHostToDevice, c->copy_stream);
     if (e == cudaSuccess) e = cudaEventRecord(h.done[hb], c->copy_stream);
     return e;
@@ -249,6 +305,14 @@ static int dataset_fill(plsb_ctx *c, const double *X, int64_t ldx, int64_t N, in
         }
     }
     if (rc != PLSB_OK) { plsb_dataset_destroy(ds); return rc; }
+    if (const char *tr = getenv("PLSB_TRACE")) {
+        plsb_ctx::HostStage &h = c->hstage;
+        if (*tr == '1' && h.pack_bytes > 0)
+            fprintf(stderr, "[plsb] staged upload: %.2f GB packed by %d host threads in %.3f s (%.1f GB/s), %.3f s waiting for "
+                            "the copy engine\n", h.pack_bytes / 1e9, h.pool ? h.pool->size() : 0, h.pack_s,
+                    h.pack_bytes / 1e9 / (h.pack_s > 0 ? h.pack_s : 1), h.wait_s);
+        h.pack_s = h.wait_s = h.pack_bytes = 0.0;
+    }
     *out = ds;
     return PLSB_OK;
 }

@@ -74,6 +74,11 @@ int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, 
         Gp = G.p;
     }
     StepArgs st{};
+    DevBuf wide(c);
+    if (const size_t wb = step_wide_scratch_bytes((int)M)) {
+        PLSB_TRY(wide.alloc(wb / sizeof(double), true));
+        st.wide = wide.p;
+    }
     st.K = (int)K; st.ldk = (int)ldk; st.M = (int)M; st.A = (int)A;
     st.S = S.p; st.g = g.p; st.W = Wd; st.P = Pd; st.R = Rd; st.Q = Qd;
     st.a = -1;
@@ -117,6 +122,17 @@ int fit_device(plsb_dataset *ds, int64_t A, int method, double *Wd, double *Pd, 
 
 using namespace plsb;
 
+// the N x A scores to host memory: large blocks bound for pageable memory go through the pinned staging pipeline
+static int download_scores(plsb_ctx *c, const double *Td, size_t n, double *T, bool as_complex) {
+    cudaPointerAttributes pa{};
+    const bool pinned = cudaPointerGetAttributes(&pa, T) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    const char *off = getenv("PLSB_NO_STAGE");
+    if (as_complex || (!pinned && n * 8 >= ((size_t)8 << 20) && !(off && *off == '1'))) return download_staged(c, Td, n, T, as_complex);
+    PLSB_CUDA(cudaMemcpyAsync(T, Td, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    return PLSB_OK;
+}
+
 extern "C" {
 
 int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, double *R, double *Q, double *T) {
@@ -146,7 +162,7 @@ int plsb_fit(plsb_dataset_t ds, int64_t A, int method, double *W, double *P, dou
     if (P) PLSB_CUDA(cudaMemcpy2DAsync(P, kb, Pd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
     if (R) PLSB_CUDA(cudaMemcpy2DAsync(R, kb, Rd.p, lb, kb, (size_t)A, cudaMemcpyDeviceToHost, c->stream));
     if (Q) PLSB_CUDA(cudaMemcpyAsync(Q, Qd.p, (size_t)A * M * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
-    if (wantT && !streamT) PLSB_CUDA(cudaMemcpyAsync(T, Td.p, (size_t)A * N * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    if (wantT && !streamT) PLSB_TRY(download_scores(c, Td.p, (size_t)A * N, T, false));
     if (streamT) PLSB_CUDA(cudaStreamSynchronize(c->copy_stream));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
     if (ds->sharded) PLSB_TRY(xchg_check(c));
@@ -198,8 +214,18 @@ int plsb_model_download(plsb_model_t m, double *W, double *P, double *R, double 
     if (Q) PLSB_CUDA(cudaMemcpyAsync(Q, m->Q, A * m->M * 8, cudaMemcpyDeviceToHost, c->stream));
     if (T) {
         PLSB_ARG(m->T, "this model holds no scores (KERNEL_TYPE2 stores none, pls.cpp:394)");
-        PLSB_CUDA(cudaMemcpyAsync(T, m->T, A * m->N * 8, cudaMemcpyDeviceToHost, c->stream));
+        PLSB_TRY(download_scores(c, m->T, A * (size_t)m->N, T, false));
     }
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
+}
+
+int plsb_model_download_scores(plsb_model_t m, double *T, int as_complex) {
+    PLSB_ARG(m && T, "null argument");
+    PLSB_ARG(m->T, "this model holds no scores (KERNEL_TYPE2 stores none, pls.cpp:394)");
+    plsb_ctx *c = m->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    PLSB_TRY(download_scores(c, m->T, (size_t)m->A * (size_t)m->N, T, as_complex != 0));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
     return PLSB_OK;
 }
@@ -249,6 +275,41 @@ int plsb_xtx(plsb_dataset_t ds, double *XX) {
     if (XX) PLSB_CUDA(cudaMemcpy2DAsync(XX, (size_t)K * 8, G.p, (size_t)ldg * 8, (size_t)K * 8, (size_t)K,
                                         cudaMemcpyDeviceToHost, c->stream));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    return PLSB_OK;
+}
+
+// Build XX = X'X and XY = X'Y once and keep them ON the data set (what an upload from host memory accumulates under the
+// transfer, dataset.cu): cross-validation calls and fits that follow start from them.  across_ranks (a REPLICATED data
+// set on a context with a communicator; collective — every rank calls it): rank g forms the cross products of rows
+// [g N/G, (g+1) N/G) only and the partial matrices are summed over the ranks (one all-reduce of K*K + K*M doubles)
+// instead of every rank reading all of X.
+int plsb_dataset_build_gram(plsb_dataset_t ds, int across_ranks) {
+    PLSB_ARG(ds, "dataset is null");
+    PLSB_ARG(!ds->sharded, "a row shard keeps partial cross products through its upload; this call is for whole data sets");
+    plsb_ctx *c = ds->ctx;
+    PLSB_CUDA(cudaSetDevice(c->device));
+    if (ds->G && ds->S0 && ds->gram_valid) return PLSB_OK;
+    const int64_t K = ds->K, ldk = ds->ldk, M = ds->M;
+    const int64_t ldg = round_up(K, 2);
+    if (!ds->G) PLSB_TRY(dev_alloc(c, (void **)&ds->G, (size_t)K * ldg * sizeof(double)));
+    if (!ds->S0) PLSB_TRY(dev_alloc(c, (void **)&ds->S0, (size_t)M * ldk * sizeof(double)));
+    ds->ldg = ldg;
+    const bool split = across_ranks && c->nranks > 1;
+    plsb_dataset view = *ds;           // this rank's rows (all of them without a communicator)
+    if (split) {
+        const int64_t r0 = ds->N * c->rank / c->nranks, r1 = ds->N * (c->rank + 1) / c->nranks;
+        view.X = ds->X + r0 * ldk; view.Y = ds->Y + r0 * ds->ldm; view.N = r1 - r0;
+    }
+    PLSB_CUDA(cudaMemsetAsync(ds->G, 0, (size_t)K * ldg * sizeof(double), c->stream));
+    PLSB_TRY(launch_xtx(c, &view, ds->G, ldg));
+    PLSB_TRY(launch_xty_pass(c, &view, ds->S0));
+    if (split) {
+        PLSB_TRY(allreduce_sum(c, ds->G, (size_t)K * ldg));
+        PLSB_TRY(allreduce_sum(c, ds->S0, (size_t)M * ldk));
+    }
+    PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    ds->gram_valid = true;
+    ds->gram_reduced = true;
     return PLSB_OK;
 }
 

@@ -191,10 +191,46 @@ __device__ __forceinline__ void gt_mbar_arrive(uint64_t *bar) {
 }
 
 // SELF = false: CW consumer warps + one producer warp (warp CW).  SELF = true: no producer warp — the CW consumer warps
-// take turns (warp kt mod CW issues the copies of k-tile kt + 2 at the top of iteration kt).  A CTA of 8 warps x 168
+// take turns (warp gk mod CW issues the copies of k-tile gk + 2 at the top of iteration gk).  A CTA of 8 warps x 168
 // registers leaves a quarter of the SM's register file and 16 KB of its shared memory free, so that a memory-bound kernel
 // of another stream (the per-fold kernel of the other CV wave, cv.cu) can be co-resident and use the HBM bandwidth this
 // tensor-bound kernel leaves idle; 9 warps are allocated as 12 and take the whole register file.
+//
+// The kernel is PERSISTENT over work items (output tile x k-split): CTA b takes items b, b + gridDim.x, ...  The ring of
+// stages and its mbarrier phases run on across items (one global k-tile counter), so the copies of the next item's first
+// tiles are in flight while the warps write the finished tile out.  Launched with one CTA per work item it is the plain
+// kernel; launched with one CTA per SM (`persist`) ALL its CTAs are resident from the start, which is what lets the block
+// scheduler place the CTAs of a concurrent kernel of another stream in the resources left over — it dispatches the
+// blocks of a second kernel only once every block of the first has been dispatched.
+struct GtItem {
+    int m_base, n_base, a_cols, b_cols, tile, split, nk;
+    int64_t k_begin, k_end;
+};
+__device__ __forceinline__ GtItem gt_item(const GemmArgs &g, int w) {
+    GtItem it;
+    it.tile = w % g.ntiles; it.split = w / g.ntiles;
+    int tm, tn;
+    if (g.syrk) syrk_tile(it.tile, g.tiles_m, tm, tn);
+    else { tm = it.tile / g.tiles_n; tn = it.tile % g.tiles_n; }
+    it.m_base = tm * GM_BM; it.n_base = tn * GM_BN;
+    it.k_begin = (int64_t)it.split * g.k_per_split;
+    it.k_end = it.k_begin + g.k_per_split;
+    if (it.k_end > g.Kd) it.k_end = g.Kd;
+    it.nk = it.k_begin < it.k_end ? (int)((it.k_end - it.k_begin + GT_BK - 1) / GT_BK) : 0;
+    int a_cols = g.M - it.m_base; it.a_cols = a_cols > GM_BM ? GM_BM : (a_cols + 1) & ~1;
+    int b_cols = g.N - it.n_base; it.b_cols = b_cols > GM_BN ? GM_BN : b_cols;   // n-major: rows of the B tile
+    return it;
+}
+
+// length of work item w's slice of the reduction axis (what the loops need; the rest of GtItem is recomputed where used,
+// to keep the cursor of the pipeline in a few registers)
+__device__ __forceinline__ int gt_klen(const GemmArgs &g, int w) {
+    const int64_t k_begin = (int64_t)(w / g.ntiles) * g.k_per_split;
+    int64_t k_end = k_begin + g.k_per_split;
+    if (k_end > g.Kd) k_end = g.Kd;
+    return k_end > k_begin ? (int)(k_end - k_begin) : 0;
+}
+
 template <bool B_NMAJOR, int CW, bool SELF>
 __global__ void __launch_bounds__((CW + (SELF ? 0 : 1)) * 32) __maxnreg__(CW == 8 ? 168 : 96) dmma_tma_kernel(const GemmArgs g) {
     extern __shared__ __align__(128) char smem[];
@@ -203,15 +239,7 @@ __global__ void __launch_bounds__((CW + (SELF ? 0 : 1)) * 32) __maxnreg__(CW == 
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)GT_STAGES * STAGE);
     uint64_t *empty = full + GT_STAGES;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x % g.ntiles, split = blockIdx.x / g.ntiles;
-    int tm, tn;
-    if (g.syrk) syrk_tile(tile, g.tiles_m, tm, tn);
-    else { tm = tile / g.tiles_n; tn = tile % g.tiles_n; }
-    const int m_base = tm * GM_BM, n_base = tn * GM_BN;
-    const int64_t k_begin = (int64_t)split * g.k_per_split;
-    int64_t k_end = k_begin + g.k_per_split;
-    if (k_end > g.Kd) k_end = g.Kd;
-    const int nk = k_begin < k_end ? (int)((k_end - k_begin + GT_BK - 1) / GT_BK) : 0;
+    const int nwork = g.ntiles * g.splitk;
     if (tid == 0) {
         for (int s = 0; s < GT_STAGES; ++s) {
             mbar_init(&full[s], 1);
@@ -221,117 +249,136 @@ __global__ void __launch_bounds__((CW + (SELF ? 0 : 1)) * 32) __maxnreg__(CW == 
     }
     __syncthreads();
 
-    // ---- producer step (one whole warp): bulk copies of the valid part of each tile row of k-tile kt; rows / columns
-    // past the matrix edge are never copied (the consumers mask the k tail, and out-of-range output rows / columns are
-    // discarded) ----
-    int a_cols = g.M - m_base; a_cols = a_cols > GM_BM ? GM_BM : (a_cols + 1) & ~1;
-    int b_cols = g.N - n_base; b_cols = b_cols > GM_BN ? GM_BN : b_cols;          // n-major: rows of the B tile
-    const int b_cols2 = (b_cols + 1) & ~1;                                       // k-major: doubles per k-row
-    auto produce = [&](int kt) {
-        const int s = kt % GT_STAGES;
-        if (kt >= GT_STAGES) mbar_wait(&empty[s], (uint32_t)(((kt / GT_STAGES) - 1) & 1));
-        const int64_t k0 = k_begin + (int64_t)kt * GT_BK;
-        const int kv = (int)(k_end - k0 < GT_BK ? k_end - k0 : GT_BK);
-        const int kv2 = (kv + 1) & ~1;
-        char *sa = smem + (size_t)s * STAGE, *sb = sa + GT_A_BYTES;
-        const uint32_t bytes = (uint32_t)kv * (uint32_t)a_cols * 8u +
-                               (B_NMAJOR ? (uint32_t)b_cols * (uint32_t)kv2 * 8u : (uint32_t)kv * (uint32_t)b_cols2 * 8u);
-        if (lane == 0) mbar_arrive_expect_tx(&full[s], bytes);
-        __syncwarp();
-        if (lane < kv) {
-            bulk_g2s(sa + (size_t)lane * GT_LD * 8, g.A + (k0 + lane) * g.lda + m_base, (uint32_t)a_cols * 8u, &full[s]);
-            if (!B_NMAJOR)
-                bulk_g2s(sb + (size_t)lane * GT_LD * 8, g.B + (k0 + lane) * g.ldb + n_base, (uint32_t)b_cols2 * 8u, &full[s]);
+    // ---- producer cursor: the next k-tile to copy, as (work item, k-tile, global k-tile count).  Every warp that may
+    // issue copies advances its own copy of the cursor identically; `issue` says whether THIS warp issues the copies:
+    // bulk copies of the valid part of each tile row (rows / columns past the matrix edge are never copied: the
+    // consumers mask the k tail, and out-of-range output rows / columns are discarded) ----
+    int pw = blockIdx.x, pkt = 0, pgk = 0;
+    int pnk = pw < nwork ? (gt_klen(g, pw) + GT_BK - 1) / GT_BK : 0;
+    auto produce_next = [&](bool issue) -> bool {
+        while (pw < nwork && pkt >= pnk) {
+            pw += gridDim.x; pkt = 0;
+            if (pw < nwork) pnk = (gt_klen(g, pw) + GT_BK - 1) / GT_BK;
         }
-        if (B_NMAJOR) {
+        if (pw >= nwork) return false;
+        if (issue) {
+            const GtItem pit = gt_item(g, pw);
+            const int s = pgk % GT_STAGES;
+            if (pgk >= GT_STAGES) mbar_wait(&empty[s], (uint32_t)(((pgk / GT_STAGES) - 1) & 1));
+            const int64_t k0 = pit.k_begin + (int64_t)pkt * GT_BK;
+            const int kv = (int)(pit.k_end - k0 < GT_BK ? pit.k_end - k0 : GT_BK);
+            const int kv2 = (kv + 1) & ~1;
+            const int b_cols2 = (pit.b_cols + 1) & ~1;                             // k-major: doubles per k-row
+            char *sa = smem + (size_t)s * STAGE, *sb = sa + GT_A_BYTES;
+            const uint32_t bytes = (uint32_t)kv * (uint32_t)pit.a_cols * 8u +
+                                   (B_NMAJOR ? (uint32_t)pit.b_cols * (uint32_t)kv2 * 8u : (uint32_t)kv * (uint32_t)b_cols2 * 8u);
+            if (lane == 0) mbar_arrive_expect_tx(&full[s], bytes);
+            __syncwarp();
+            if (lane < kv) {
+                bulk_g2s(sa + (size_t)lane * GT_LD * 8, g.A + (k0 + lane) * g.lda + pit.m_base, (uint32_t)pit.a_cols * 8u, &full[s]);
+                if (!B_NMAJOR)
+                    bulk_g2s(sb + (size_t)lane * GT_LD * 8, g.B + (k0 + lane) * g.ldb + pit.n_base, (uint32_t)b_cols2 * 8u, &full[s]);
+            }
+            if (B_NMAJOR) {
 #pragma unroll
-            for (int i = 0; i < GM_BN / 32; ++i) {
-                const int n = lane + 32 * i;
-                if (n < b_cols)
-                    bulk_g2s(sb + (size_t)n * GT_LDBN * 8, g.B + (int64_t)(n_base + n) * g.ldb + k0, (uint32_t)kv2 * 8u, &full[s]);
+                for (int i = 0; i < GM_BN / 32; ++i) {
+                    const int n = lane + 32 * i;
+                    if (n < pit.b_cols)
+                        bulk_g2s(sb + (size_t)n * GT_LDBN * 8, g.B + (int64_t)(pit.n_base + n) * g.ldb + k0, (uint32_t)kv2 * 8u, &full[s]);
+                }
             }
         }
+        ++pkt; ++pgk;
+        return true;
     };
     if (!SELF && warp == CW) {
-        for (int kt = 0; kt < nk; ++kt) produce(kt);
+        while (produce_next(true)) {}
         return;
     }
-    if (SELF && warp < GT_STAGES - 1 && warp < nk) produce(warp);     // prologue: tiles 0 and 1 by warps 0 and 1
+    if (SELF) {   // prologue: the first STAGES - 1 k-tiles of this CTA, by warps 0 .. STAGES - 2
+#pragma unroll
+        for (int i = 0; i < GT_STAGES - 1; ++i) produce_next(warp == i);
+    }
 
     // ---- consumers ------------------------------------------------------------------------------------------------
-    double acc[MI][4][2];
-#pragma unroll
-    for (int i = 0; i < MI; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
     const int wm = (warp >> 2) * WM, wn = (warp & 3) * 32;
     const int fk = lane & 3, fr = lane >> 2;
-    for (int kt = 0; kt < nk; ++kt) {
-        const int s = kt % GT_STAGES;
-        if (SELF && warp == (kt % CW) && kt + GT_STAGES - 1 < nk) produce(kt + GT_STAGES - 1);   // the stage freed by tile kt - 1
-        mbar_wait(&full[s], (uint32_t)((kt / GT_STAGES) & 1));
-        const double *as = reinterpret_cast<const double *>(smem + (size_t)s * STAGE) + fk * GT_LD + wm + fr;
-        const double *bs = reinterpret_cast<const double *>(smem + (size_t)s * STAGE + GT_A_BYTES) +
-                           (B_NMAJOR ? (wn + fr) * GT_LDBN + fk : fk * GT_LD + wn + fr);
-        const int64_t kleft = k_end - (k_begin + (int64_t)kt * GT_BK);
-        if (kleft >= GT_BK) {
-#pragma unroll
-            for (int kk = 0; kk < GT_BK / 4; ++kk) {
-                double a[MI], b[4];
-#pragma unroll
-                for (int i = 0; i < MI; ++i) a[i] = as[kk * 4 * GT_LD + i * 8];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) b[j] = B_NMAJOR ? bs[j * 8 * GT_LDBN + kk * 4] : bs[kk * 4 * GT_LD + j * 8];
-#pragma unroll
-                for (int i = 0; i < MI; ++i)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
-            }
-        } else {   // last k-tile of a split: rows past the end were not copied and hold stale shared memory
-            const int kv = (int)kleft;
-#pragma unroll 1
-            for (int kk = 0; kk * 4 < kv; ++kk) {
-                const bool live = kk * 4 + fk < kv;
-                double a[MI], b[4];
-#pragma unroll
-                for (int i = 0; i < MI; ++i) a[i] = live ? as[kk * 4 * GT_LD + i * 8] : 0.0;
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    b[j] = live ? (B_NMAJOR ? bs[j * 8 * GT_LDBN + kk * 4] : bs[kk * 4 * GT_LD + j * 8]) : 0.0;
-#pragma unroll
-                for (int i = 0; i < MI; ++i)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
-            }
-        }
-        __syncwarp();
-        if (lane == 0) gt_mbar_arrive(&empty[s]);
-    }
-    if (g.splitk == 1 && !g.syrk && !g.accum) {  // no partials needed: write the product directly
+    int gk = 0;                                   // k-tiles this CTA has consumed so far (all work items)
+    for (int w = blockIdx.x; w < nwork; w += gridDim.x) {
+        const int klen = gt_klen(g, w), nk = (klen + GT_BK - 1) / GT_BK;
+        double acc[MI][4][2];
 #pragma unroll
         for (int i = 0; i < MI; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int m = m_base + wm + i * 8 + fr, n = n_base + wn + j * 8 + fk * 2;
-                if (m >= g.M) continue;
-                if (!g.transC) {
-                    if (n < g.N) g.C[(int64_t)m * g.ldc + n] = acc[i][j][0];
-                    if (n + 1 < g.N) g.C[(int64_t)m * g.ldc + n + 1] = acc[i][j][1];
-                } else {
-                    if (n < g.N) g.C[(int64_t)n * g.ldc + m] = acc[i][j][0];
-                    if (n + 1 < g.N) g.C[(int64_t)(n + 1) * g.ldc + m] = acc[i][j][1];
+            for (int j = 0; j < 4; ++j) { acc[i][j][0] = 0.0; acc[i][j][1] = 0.0; }
+        for (int kt = 0; kt < nk; ++kt, ++gk) {
+            const int s = gk % GT_STAGES;
+            if (SELF) produce_next(warp == (gk % CW));   // k-tile gk + STAGES - 1, into the stage freed by k-tile gk - 1
+            mbar_wait(&full[s], (uint32_t)((gk / GT_STAGES) & 1));
+            const double *as = reinterpret_cast<const double *>(smem + (size_t)s * STAGE) + fk * GT_LD + wm + fr;
+            const double *bs = reinterpret_cast<const double *>(smem + (size_t)s * STAGE + GT_A_BYTES) +
+                               (B_NMAJOR ? (wn + fr) * GT_LDBN + fk : fk * GT_LD + wn + fr);
+            const int kleft = klen - kt * GT_BK;
+            if (kleft >= GT_BK) {
+#pragma unroll
+                for (int kk = 0; kk < GT_BK / 4; ++kk) {
+                    double a[MI], b[4];
+#pragma unroll
+                    for (int i = 0; i < MI; ++i) a[i] = as[kk * 4 * GT_LD + i * 8];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) b[j] = B_NMAJOR ? bs[j * 8 * GT_LDBN + kk * 4] : bs[kk * 4 * GT_LD + j * 8];
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                }
+            } else {   // last k-tile of a split: rows past the end were not copied and hold stale shared memory
+                const int kv = kleft;
+#pragma unroll 1
+                for (int kk = 0; kk * 4 < kv; ++kk) {
+                    const bool live = kk * 4 + fk < kv;
+                    double a[MI], b[4];
+#pragma unroll
+                    for (int i = 0; i < MI; ++i) a[i] = live ? as[kk * 4 * GT_LD + i * 8] : 0.0;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        b[j] = live ? (B_NMAJOR ? bs[j * 8 * GT_LDBN + kk * 4] : bs[kk * 4 * GT_LD + j * 8]) : 0.0;
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
                 }
             }
-        return;
-    }
-    double *out = g.part + ((size_t)split * g.ntiles + tile) * (GM_BM * GM_BN);
-#pragma unroll
-    for (int i = 0; i < MI; ++i)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int row = wm + i * 8 + fr, col = wn + j * 8 + fk * 2;
-            *reinterpret_cast<double2 *>(out + row * GM_BN + col) = make_double2(acc[i][j][0], acc[i][j][1]);
+            __syncwarp();
+            if (lane == 0) gt_mbar_arrive(&empty[s]);
         }
+        const GtItem it = gt_item(g, w);
+        if (g.splitk == 1 && !g.syrk && !g.accum) {  // no partials needed: write the product directly
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int m = it.m_base + wm + i * 8 + fr, n = it.n_base + wn + j * 8 + fk * 2;
+                    if (m >= g.M) continue;
+                    if (!g.transC) {
+                        if (n < g.N) g.C[(int64_t)m * g.ldc + n] = acc[i][j][0];
+                        if (n + 1 < g.N) g.C[(int64_t)m * g.ldc + n + 1] = acc[i][j][1];
+                    } else {
+                        if (n < g.N) g.C[(int64_t)n * g.ldc + m] = acc[i][j][0];
+                        if (n + 1 < g.N) g.C[(int64_t)(n + 1) * g.ldc + m] = acc[i][j][1];
+                    }
+                }
+        } else {
+            double *out = g.part + ((size_t)it.split * g.ntiles + it.tile) * (GM_BM * GM_BN);
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int row = wm + i * 8 + fr, col = wn + j * 8 + fk * 2;
+                    *reinterpret_cast<double2 *>(out + row * GM_BN + col) = make_double2(acc[i][j][0], acc[i][j][1]);
+                }
+        }
+    }
 }
 
 // C[m*ldc + n] = sum_s part[s][tile][...]; SYRK also writes the mirrored element
@@ -357,7 +404,7 @@ __global__ void __launch_bounds__(256) gemm_reduce_kernel(const GemmArgs g, doub
 // transC: store C transposed (N x M, row-major).
 int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
                     double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate,
-                    GemmLane *lane) {
+                    GemmLane *lane, bool no_split) {
     if (M == 0 || N == 0) return PLSB_OK;
     PLSB_ARG((lda % 2) == 0 && (ldb % 2) == 0, "gemm: leading dimensions must be even");
     cudaStream_t st = lane ? lane->stream : c->stream;
@@ -372,6 +419,7 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
     // x 13 splits = 1768 CTAs = 11.95 waves instead of 5 splits = 4.59; a 2500-fold CV wave: 640 tiles x 2).
     int64_t maxsplit = ceil_div(Kd, (int64_t)GM_BK * 64);
     if (maxsplit > 64) maxsplit = 64;
+    if (no_split) maxsplit = 1;   // the caller wants sums that do not depend on the batch width (cv.cu)
     int64_t want = 1;
     double best_eff = -1.0;
     for (int64_t sp = 1; sp <= maxsplit; ++sp) {
@@ -407,6 +455,7 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
     }();
     static const int self_env = [] { const char *e = getenv("PLSB_GEMM_SELF"); return e ? atoi(e) : -1; }();
     const bool self = self_env >= 0 ? self_env != 0 : lane != nullptr;
+    static const int persist_env = [] { const char *e = getenv("PLSB_GEMM_PERSIST"); return e ? atoi(e) : -1; }();
     if (b_nmajor) PLSB_ARG(ldb >= round_up(Kd, 2), "gemm: an n-major B needs ldb >= Kd rounded up to even");
     if (variant == 1) {
         const size_t smem = (size_t)GM_STAGES * (GM_BK * GM_LD + (b_nmajor ? GM_BS_NMAJOR : GM_BS_KMAJOR)) * sizeof(double);
@@ -422,8 +471,13 @@ int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, 
         else if (self) { kern = b_nmajor ? dmma_tma_kernel<true, 8, true> : dmma_tma_kernel<false, 8, true>; threads = 8 * 32; }
         else { kern = b_nmajor ? dmma_tma_kernel<true, 8, false> : dmma_tma_kernel<false, 8, false>; threads = 9 * 32; }
         PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // one CTA per SM looping over the work items when another stream is to co-run (see the kernel's header);
+        // PLSB_GEMM_PERSIST=0/1 forces either shape (A/B)
+        const bool persist = persist_env >= 0 ? persist_env != 0 : lane != nullptr;
+        unsigned grid = (unsigned)(g.ntiles * g.splitk);
+        if (persist && grid > (unsigned)c->sm_count) grid = (unsigned)c->sm_count;
         ProfScope ps(c, lane ? -1 : prof_slot);
-        kern<<<(unsigned)(g.ntiles * g.splitk), threads, smem, st>>>(g);
+        kern<<<grid, threads, smem, st>>>(g);
     }
     PLSB_CUDA(cudaGetLastError());
     c->launches += 1;

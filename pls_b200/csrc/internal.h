@@ -47,9 +47,15 @@ struct plsb_ctx {
         size_t bytes = 0;
         cudaEvent_t done[3] = {nullptr, nullptr, nullptr};   // "the H2D copy that read buf[i] has finished"
         plsb::HostPool *pool = nullptr;
+        double pack_s = 0, wait_s = 0, pack_bytes = 0;       // PLSB_TRACE=1: where a staged upload spent its time
+        // the way back: two pinned (cached, NOT write-combined: the CPU reads them) buffers for large D2H results
+        char *dbuf[2] = {nullptr, nullptr};
+        size_t dbytes = 0;
+        cudaEvent_t ddone[2] = {nullptr, nullptr};
     } hstage;
     // profiling
-    int prof = 0;   // 0 off, 1 an event pair around every launch group, 2 only around whole fits (PLSB_PROF_FIT_TOTAL)
+    int prof = 0;   // 0 off, 1 an event pair around every launch group, 2 only around whole fits (PLSB_PROF_FIT_TOTAL),
+                    // 3 like 1 but the two-lane CV engine keeps both lanes (its kernels are timed IN the overlap)
     struct Pending { int slot; cudaEvent_t a, b; };
     std::vector<Pending> pending;
     std::vector<cudaEvent_t> pool;
@@ -110,6 +116,12 @@ int launch_reduce_partials(plsb_ctx *c, const double *part, int64_t ld, int nb, 
 int xchg_setup(plsb_ctx *c, int (*allgather)(plsb_ctx *, const void *, void *, size_t));
 void xchg_teardown(plsb_ctx *c);
 int xchg_check(plsb_ctx *c);  // error if an exchange timed out
+// n contiguous doubles from device memory to PAGEABLE host memory at copy-engine speed: chunks go to pinned staging
+// buffers on the copy stream (after everything queued on c->stream so far) and a pool of host threads moves chunk i
+// out while chunk i+1 is in flight.  as_complex: the destination is n (re, im) pairs, im = 0 — the reference's model
+// matrices are complex-typed (pls.h:251-254), so the widening costs no extra pass over host memory.
+// A cudaMemcpy into pageable memory runs at 2-3 GB/s here (measured: 256 MB of scores in 0.1 s).
+int download_staged(plsb_ctx *c, const double *dev, size_t n, double *host, bool as_complex);
 // upload a host column-major matrix into a device row-major one (staged, chunked by columns)
 int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, int64_t cols, double *dst, int64_t ldd,
                     bool src_on_device);
@@ -117,8 +129,9 @@ int upload_cm_to_rm(plsb_ctx *c, const double *src, int64_t lds, int64_t rows, i
 // RAII-ish profiling scope: records events around a launch group when profiling is on
 struct ProfScope {
     plsb_ctx *c;
+    cudaStream_t st;
     int idx = -1;
-    ProfScope(plsb_ctx *ctx, int slot);
+    ProfScope(plsb_ctx *ctx, int slot, cudaStream_t stream = nullptr);   // stream: where the launch group goes (default: the context's)
     ~ProfScope();
 };
 
@@ -149,7 +162,9 @@ struct StepArgs {
     double *W, *P, *R; // A x ldk each (column a at [a*ldk])
     double *Q;         // A x M
     long long *trace;  // dev tool (PLSB_STEP_TRACE): globaltimer ns at phase boundaries, or null
+    double *wide;      // M > 32 (step_wide.cuh): wide_scratch_doubles(M) doubles of device scratch, else null
 };
+size_t step_wide_scratch_bytes(int M);   // 0 when M <= 32
 int launch_step(plsb_ctx *c, const StepArgs &s);
 
 // y = G r, tt = r'G r for symmetric G (K x K, ld = ldg): KERNEL_TYPE2 per-component product
@@ -161,10 +176,24 @@ int launch_symv(plsb_ctx *c, const double *G, int64_t ldg, int K, const double *
 struct GemmLane { cudaStream_t stream = nullptr; double *part = nullptr; size_t part_bytes = 0; };
 int launch_gemm_atb(plsb_ctx *c, const double *A, int64_t lda, const double *B, int64_t ldb, int64_t Kd, int M, int N,
                     double *C, int64_t ldc, bool syrk, bool b_nmajor, bool transC, int prof_slot, bool accumulate = false,
-                    GemmLane *lane = nullptr);
+                    GemmLane *lane = nullptr, bool no_split = false);
 // S (component-major A x lds) = X R for row-major X (N x ldk) and component-major R (A x ldk): DMMA (scores.cu)
 int launch_scores(plsb_ctx *c, const double *X, int64_t N, int ldk, const double *R, int A, double *S, int64_t lds);
 int launch_xtx(plsb_ctx *c, const plsb_dataset *ds, double *G, int64_t ldg);
+
+// ---- batched-fold product of the two-lane CV engine (cv_gemm.cu): persistent DMMA kernel over PRE-TILED operands ----
+// Gt: [m-tile][k-tile][32][132] copy of X'X; Rt: [n-tile][k-tile][128][36] the wave's current r vectors, written in
+// this layout by the fold kernels (element (f, k) at cv_gemm_rt_index)
+constexpr int CVG_BN = 128, CVG_BK = 32, CVG_LDB = 36;
+#ifdef __CUDACC__
+__host__ __device__ inline size_t cv_gemm_rt_index(int nkt, int f, int k) {
+    return (((size_t)(f / CVG_BN) * nkt + (size_t)(k / CVG_BK)) * CVG_BN + (size_t)(f % CVG_BN)) * CVG_LDB + (size_t)(k % CVG_BK);
+}
+#endif
+size_t cv_gemm_gt_doubles(int64_t K);
+size_t cv_gemm_rt_doubles(int64_t K, int64_t F);
+int launch_cv_gemm_tile_g(plsb_ctx *c, cudaStream_t st, const double *G, int64_t ldg, int64_t K, double *Gt);
+int launch_cv_gemm(plsb_ctx *c, cudaStream_t st, const double *Gt, const double *Rt, int64_t K, int64_t ldk, int nf, double *Gr);
 
 // ---- synthetic data (synth.cu) ----------------------------------------------------------------
 int launch_synth(plsb_ctx *c, uint64_t seed, int64_t row0, int64_t N, int64_t K, int64_t M, int64_t L,

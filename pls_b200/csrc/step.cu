@@ -9,6 +9,7 @@
 #include "internal.h"
 #include "step_cluster.cuh"
 #include "step_core.cuh"
+#include "step_wide.cuh"
 
 namespace plsb {
 
@@ -24,6 +25,19 @@ __global__ void __launch_bounds__(STEP_NT) step_kernel(const StepArgs s) {
     if (an >= s.A) return;
     next_weights<STEP_NT>(s.K, ldk, s.M, an, s.S, s.P, s.R, s.W + (size_t)an * ldk, s.R + (size_t)an * ldk, sh);
 }
+
+// Wide response blocks (M > 32): the general path of step_wide.cuh, one CTA, M-sized objects in global scratch.
+__global__ void __launch_bounds__(STEP_NT) step_wide_kernel(const StepArgs s) {
+    __shared__ WideSmem<STEP_NT> sh;
+    const int ldk = s.ldk;
+    if (s.a >= 0)
+        finish_component_wide<STEP_NT>(s.K, ldk, s.M, s.S, s.g, s.g[ldk], s.R + (size_t)s.a * ldk, s.P + (size_t)s.a * ldk,
+                                       s.Q + (size_t)s.a * s.M, s.wide);
+    const int an = s.a + 1;
+    if (an >= s.A) return;
+    next_weights_wide<STEP_NT>(s.K, ldk, s.M, an, s.S, s.P, s.R, s.W + (size_t)an * ldk, s.R + (size_t)an * ldk, s.wide, sh);
+}
+size_t step_wide_scratch_bytes(int M) { return M > PLSB_MAX_M ? wide_scratch_doubles(M) * sizeof(double) : 0; }
 
 // ------------------------------------------------------------------------------------------------
 // The step as a thread-block CLUSTER: 8 CTAs on 8 SMs, each owning a slice of the K axis.
@@ -377,9 +391,15 @@ static int launch_step_cluster(plsb_ctx *c, const StepArgs &s) {
 }
 
 int launch_step(plsb_ctx *c, const StepArgs &s) {
-    if (s.M > PLSB_MAX_M) {
-        set_error("M=%d responses exceed the in-kernel eigen solver limit (%d)", s.M, PLSB_MAX_M);
-        return PLSB_ERR_UNSUPPORTED;
+    if (s.M > PLSB_MAX_M) {   // wide response block: the general one-CTA path
+        PLSB_ARG(s.wide, "internal: no scratch for the wide-response step");
+        {
+            ProfScope ps(c, PLSB_PROF_STEP);
+            step_wide_kernel<<<1, STEP_NT, 0, c->stream>>>(s);
+        }
+        c->launches++;
+        PLSB_CUDA(cudaGetLastError());
+        return PLSB_OK;
     }
     const bool force_v1 = getenv("PLSB_STEP_V1") != nullptr;  // A/B switch for tools/devbench.py
     if (!force_v1 && s.ldk <= SC_NCTA * SC_NT * SC_KPT && step_cl_layout(s.ldk, s.M).bytes <= c->smem_optin)

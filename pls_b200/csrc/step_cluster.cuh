@@ -123,10 +123,13 @@ __device__ __forceinline__ int squaring_loop(double *buf0, double *buf1, double 
 // find_dominant_ev's pick (largest |eigenvalue|; all are >= 0 here) up to sign.
 // G is preserved; B0, B1 (>= MP*MP doubles each, MP = m rounded up to 8/16/32) are work arrays; q receives the
 // eigenvector.  All 32 lanes must call.
+// MAXMP (8, 16 or 32): the caller guarantees m <= MAXMP; only the squaring loops up to that size are instantiated
+// (the 32-wide one keeps a 32-double row in registers: not something to inline into a 64-register kernel).
+template <int MAXMP = 32>
 __device__ __forceinline__ void dominant_eigvec_warp(const double *G, double *B0, double *B1, int m, double *q,
                                                      long long *iters = nullptr) {
     const int lane = threadIdx.x & 31;
-    const int mp = m <= 8 ? 8 : (m <= 16 ? 16 : 32);
+    const int mp = (m <= 8 || MAXMP == 8) ? 8 : ((m <= 16 || MAXMP == 16) ? 16 : 32);
     double tr = 0.0;
     for (int i = 0; i < m; ++i) tr += G[i * m + i];
     if (!(tr > 0.0) || !(tr < 1e300)) {  // S is exactly zero (components past the rank) or not finite
@@ -139,8 +142,13 @@ __device__ __forceinline__ void dominant_eigvec_warp(const double *G, double *B0
         B0[e] = (i < m && j < m) ? G[i * m + j] : 0.0;
     }
     __syncwarp();
-    const int res = mp == 8 ? squaring_loop<8>(B0, B1, tr, iters)
-                            : (mp == 16 ? squaring_loop<16>(B0, B1, tr, iters) : squaring_loop<32>(B0, B1, tr, iters));
+    int res;
+    if (mp == 8) res = squaring_loop<8>(B0, B1, tr, iters);
+    else if constexpr (MAXMP >= 16) {
+        if (mp == 16) res = squaring_loop<16>(B0, B1, tr, iters);
+        else if constexpr (MAXMP >= 32) res = squaring_loop<32>(B0, B1, tr, iters);
+        else res = -1;
+    } else res = -1;
     __syncwarp();
     if (res < 0) {
         for (int e = lane; e < m * m; e += 32) B0[e] = G[e];

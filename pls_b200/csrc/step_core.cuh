@@ -6,6 +6,7 @@
 #pragma once
 #include "common.cuh"
 #include "jacobi.cuh"
+#include "step_cluster.cuh"
 
 namespace plsb {
 
@@ -18,6 +19,16 @@ struct StepSmem {
     double red[NT / 32];
     double bc;  // broadcast slot
 };
+
+// Dominant unit eigenvector of the M x M Gram matrix in sh.gram (one warp; role of pls.cpp:406-407, 113-141).  Up to
+// 16 responses: the repeated-squaring solver of the cluster step (step_cluster.cuh; ~1-2 us, Jacobi as its own fallback
+// for near-degenerate spectra) with sh.V as its two work arrays — the Jacobi sweeps alone were 44 % of the small-data CV
+// kernel's time (ncu, profiles/r2e).  Wider blocks keep the Jacobi solver (work arrays of 32 x 32 would not fit).
+template <int NT>
+__device__ __forceinline__ void dominant_small(StepSmem<NT> &sh, int M) {
+    if (M <= 16) dominant_eigvec_warp<16>(sh.gram, sh.V, sh.V + 256, M, sh.q);
+    else jacobi_dominant_warp(sh.gram, sh.V, M, sh.q);
+}
 
 // one warp per dot product, lanes stride the K axis; out[d] = a_d . b_d
 template <int NT, typename FA, typename FB>
@@ -102,7 +113,7 @@ __device__ __forceinline__ void next_weights(int K, int ldk, int M, int an, cons
             }
         }
         __syncthreads();
-        if (warp == 0) jacobi_dominant_warp(sh.gram, sh.V, M, sh.q);
+        if (warp == 0) dominant_small<NT>(sh, M);
         __syncthreads();
         for (int k = tid; k < ldk; k += NT) {
             double acc = 0.0;

@@ -6,7 +6,10 @@
 // coefficients, fitted_values, residuals, SSE, explained_variance), 469-549 (cv_LOO, cv_NEW_DATA,
 // cv_LSO), 551-580 (print_explained_variance, print_state).
 #include <cassert>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <iomanip>
 #include <thread>
 
@@ -76,13 +79,20 @@ void Model::fit_on(DeviceMirror &data, const Mat2D &X, const Mat2D &Y, const MET
     const int meth = algorithm == KERNEL_TYPE2 ? PLSB_KERNEL_TYPE2 : PLSB_KERNEL_TYPE1;
     const bool wantT = algorithm == KERNEL_TYPE1;
     Mat2D Wr(K, A), Pr(K, A), Rr(K, A), Qr(M, A), Tr;
-    if (wantT) Tr.resize(N, A);
     const size_t ndev = e.ndev();
+    bool direct_T = false;
+    const char *trace = getenv("PLSB_TRACE");
+    const auto t_start = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (trace && *trace == '1')
+            fprintf(stderr, "[pls] fit_on: %s at %.3f s\n", what, std::chrono::duration<double>(std::chrono::steady_clock::now() - t_start).count());
+    };
     if (ndev > 1 && N >= e.shard_min_rows) {
         // row-sharded fit: every GPU streams its rows, K-length partials are all-reduced.  The shards
         // stay: together they are the model's copy of the training data (cv_* gathers them device to device).
         e.ensure_comm();
         data.load_shards(X.data(), ld(X), Y.data(), ld(Y));
+        if (wantT) Tr.resize(N, A);
         std::vector<Mat2D> Tpart(ndev);
         e.parallel([&](size_t i) {
             const int64_t rows = data.shard_row0[i + 1] - data.shard_row0[i];
@@ -94,18 +104,32 @@ void Model::fit_on(DeviceMirror &data, const Mat2D &X, const Mat2D &Y, const MET
         if (wantT)
             for (size_t i = 0; i < ndev; ++i) Tr.middleRows(data.shard_row0[i], Tpart[i].rows()) = Tpart[i];
     } else {
+        // one GPU: the fit's results are formed in HBM (resident model); the K-sized matrices come home as they are, the
+        // N x A scores go straight from the transfer's staging buffers into the complex-typed member T
         data.load_full(X.data(), ld(X), Y.data(), ld(Y));
-        ok(plsb_fit(data.full[0], (int64_t)A, meth, Wr.data(), Pr.data(), Rr.data(), Qr.data(), wantT ? Tr.data() : nullptr),
-           "plsb_fit");
+        lap("data set in HBM");
+        plsb_model_t mh = nullptr;
+        ok(plsb_fit_resident(data.full[0], (int64_t)A, meth, &mh), "plsb_fit_resident");
+        lap("fit done");
+        int rc = plsb_model_download(mh, Wr.data(), Pr.data(), Rr.data(), Qr.data(), nullptr);
+        if (rc == PLSB_OK && wantT) {
+            T.resize(N, A);
+            rc = plsb_model_download_scores(mh, reinterpret_cast<double *>(T.data()), 1);
+            direct_T = true;
+        }
+        plsb_model_destroy(mh);
+        ok(rc, "plsb_model_download");
     }
+    lap("fit done, results on the host");
     W = as_complex(Wr);
     P = as_complex(Pr);
     R = as_complex(Rr);
     Q = as_complex(Qr);
-    if (wantT) {  // KERNEL_TYPE2 leaves T as it was (pls.cpp:394, 434)
+    if (wantT && !direct_T) {  // KERNEL_TYPE2 leaves T as it was (pls.cpp:394, 434)
         T.resize(N, A);
         Engine::widen(Tr.data(), T.data(), (size_t)N * A);
     }
+    lap("complex-typed members filled");
 }
 
 // ---- prediction helpers (pls.cpp:439-467) ---------------------------------------------------------

@@ -81,7 +81,9 @@ def test_c5s_loo(ctx):
                                            (64, 130, 8, 4, 3, 50), (700, 20, 2, 4, 300, 3),
                                            # K >= 1024: the fused per-component fold kernel, every M variant
                                            (90, 1100, 3, 5, 1, 40), (60, 2049, 1, 4, 7, 12), (50, 4096, 8, 4, 2, 9),
-                                           (70, 1024, 2, 6, 20, 6), (40, 1500, 5, 9, 1, 40)])
+                                           (70, 1024, 2, 6, 20, 6), (40, 1500, 5, 9, 1, 40),
+                                           # M > 32: per-fold scratch in global memory (step_wide.cuh)
+                                           (80, 45, 36, 4, 3, 12), (60, 1100, 34, 3, 1, 10)])
 def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
     X, Y = port.synth(500 + N + K, N, K, M, L=max(A, 4))
     rng = np.random.default_rng(N)
@@ -116,6 +118,58 @@ def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
     assert relerr(press, _capi.validation(got, 0)) <= 1e-13
     p0 = ds.cv_press(A, 0, te, fold0=0, nfolds_local=h); p1 = ds.cv_press(A, 0, te, fold0=h, nfolds_local=nf - h)
     assert relerr(p0 + p1, press) <= 1e-13
+    ds.close()
+
+
+@pytest.mark.parametrize("N,K,M,A", [(2600, 2200, 2, 4), (900, 37, 3, 5), (640, 1030, 1, 3)])
+def test_two_lane_engine_equals_one_lane_and_the_oracle(ctx, N, K, M, A, monkeypatch):
+    """>= 512 folds run as two waves in flight (GEMM of one lane under the fold kernel of the other, persistent self-fed
+    TMA GEMM looping over > 148 work items); one lane on the context's stream is the A/B reference.  Folds are
+    independent and every kernel is deterministic, so the two schedules must agree bit for bit; a sample of folds is
+    checked against explicit refits by the oracle."""
+    import os
+    monkeypatch.setenv("PLSB_CV_NO_SMALL", "1")     # (the small shape would otherwise run as one launch out of shared memory)
+    X, Y = port.synth(991, N, K, M, L=4)
+    ds = _capi.Dataset(ctx, X, Y)
+    te = loo_idx(N)
+    two = ds.cv_folds(A, 0, te)
+    os.environ["PLSB_CV_LANES"] = "1"
+    try:
+        one = ds.cv_folds(A, 0, te)
+    finally:
+        del os.environ["PLSB_CV_LANES"]
+    assert np.array_equal(one, two)
+    os.environ["PLSB_FOLD_BATCH"] = "300"       # several rounds of two waves, a ragged last one
+    try:
+        assert np.array_equal(ds.cv_folds(A, 0, te), two)
+    finally:
+        del os.environ["PLSB_FOLD_BATCH"]
+    pick = np.array([0, 1, N // 2 - 1, N // 2, N // 2 + 107, N // 2 + 108, N - 1], dtype=np.int64)
+    want = port.cv_folds(X, Y, A, 0, te[pick])
+    assert relerr(two[:, pick, :], want) <= RTOL
+    press = ds.cv_press(A, 0, te)
+    assert relerr(press, (two ** 2).sum(axis=1)) <= 1e-13
+    ds.close()
+
+
+def test_cross_products_kept_on_the_data_set(ctx, monkeypatch):
+    """plsb_dataset_build_gram: X'X and X'Y are built once and kept; cv calls (and fits) start from them."""
+    monkeypatch.setenv("PLSB_CV_NO_SMALL", "1")
+    N, K, M, A = 300, 140, 2, 5
+    X, Y = port.synth(77, N, K, M, L=4)
+    ds = _capi.Dataset(ctx, synth=(77, 0, N, K, M, 4))
+    te = loo_idx(N)
+    before = ds.cv_folds(A, 0, te)
+    ds.build_gram()
+    ctx.profile(True); ctx.profile_reset()
+    after = ds.cv_folds(A, 0, te)
+    assert ctx.profile_get("xtx")[1] == 0                 # not rebuilt by the call
+    ctx.profile(False)
+    assert np.array_equal(before, after)
+    assert relerr(after[:, :40, :], port.cv_folds(X, Y, A, 0, te[:40])) <= RTOL
+    got = ds.fit(A, 0)                                    # a fit from the kept X'X (KERNEL_TYPE2 recurrence) + T = X R
+    want = port.fit(X, Y, A, 0)
+    assert relerr(port.coefficients(got["R"], got["Q"], A), port.coefficients(want["R"], want["Q"], A)) <= RTOL
     ds.close()
 
 

@@ -78,7 +78,8 @@ def test_fit_synthetic_matches_reference_golden(ctx, name, method):
 SHAPES = [(3, 2, 1, 1), (40, 7, 1, 5), (33, 12, 2, 6), (257, 64, 3, 6), (200, 100, 5, 9), (64, 130, 8, 5),
           (300, 255, 2, 7), (129, 401, 3, 8), (90, 513, 2, 6), (150, 1000, 4, 6), (70, 1500, 2, 5),
           (64, 2048, 8, 6), (50, 2500, 3, 5), (40, 4096, 4, 6), (2000, 31, 9, 9),
-          (30, 5000, 2, 4), (25, 9001, 3, 4), (600, 4100, 12, 5)]   # wide: the two-kernel fallback pass, M > 8
+          (30, 5000, 2, 4), (25, 9001, 3, 4), (600, 4100, 12, 5),   # wide: the two-kernel fallback pass, M > 8
+          (120, 50, 40, 5), (300, 600, 33, 4), (90, 70, 65, 3)]     # M > 32: the general step (step_wide.cuh)
 
 
 @pytest.mark.parametrize("N,K,M,A", SHAPES)

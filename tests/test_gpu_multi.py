@@ -131,6 +131,43 @@ def test_fold_sharded_cv_matches_single_gpu():
 
 
 @needs2
+def test_cross_products_built_across_ranks_for_fold_sharded_cv(monkeypatch):
+    """plsb_dataset_build_gram(across_ranks): every rank holds the whole data set (folds are sharded) but reads only its
+    row slice for X'X / X'Y; the partial matrices are all-reduced.  Residuals agree with the single-GPU call (summation
+    order differs: 1e-11) and with the oracle's explicit refits."""
+    monkeypatch.setenv("PLSB_CV_NO_SMALL", "1")
+    G = 2
+    seed, N, K, M, A = 31, 1200, 260, 2, 6
+    X, Y = port.synth(seed, N, K, M, L=4)
+    te = np.arange(N, dtype=np.int64).reshape(-1, 1)
+    ctxs = [_capi.Context(i) for i in range(G)]
+    uid = _capi.Context.unique_id()
+    E = np.zeros((M, A, N))
+    fb = shard_bounds(N, G)
+    ok = [False] * G
+
+    def rank(i):
+        ctxs[i].comm_init(i, G, uid)
+        ds = _capi.Dataset(ctxs[i], synth=(seed, 0, N, K, M, 4))
+        ds.build_gram(across_ranks=True)
+        ctxs[i].profile(True); ctxs[i].profile_reset()
+        ds.cv_folds(A, 0, te, fold0=fb[i], nfolds_local=fb[i + 1] - fb[i], out=E)
+        ok[i] = ctxs[i].profile_get("xtx")[1] == 0
+        ctxs[i].profile(False)
+        ds.close()
+
+    th = [threading.Thread(target=rank, args=(i,)) for i in range(G)]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert all(ok)
+    Em = E.transpose(0, 2, 1)
+    single = _capi.Dataset(ctxs[0], synth=(seed, 0, N, K, M, 4)).cv_folds(A, 0, te)
+    assert relerr(Em, single) <= 1e-11
+    pick = np.array([0, 599, 600, 1199])
+    assert relerr(Em[:, pick, :], port.cv_folds(X, Y, A, 0, te[pick])) <= RTOL
+    [c.close() for c in ctxs]
+
+
+@needs2
 def test_cpp_layer_multi_gpu(tmp_path):
     from tests.test_gpu_cpp_api import API_CHECK, run_api_check, stacked
     if not os.path.exists(API_CHECK):

@@ -10,7 +10,8 @@ pytestmark = pytest.mark.skipif(not ref.available(), reason="oracle/_ref not bui
 
 
 @pytest.mark.parametrize("N,K,M,A", [(40, 7, 1, 5), (33, 12, 2, 6), (200, 31, 5, 9), (17, 17, 3, 4), (64, 5, 8, 5),
-                                     (3, 2, 1, 1), (50, 9, 9, 6)])
+                                     (3, 2, 1, 1), (50, 9, 9, 6),
+                                     (120, 50, 40, 5), (90, 70, 33, 4)])    # wide response blocks (M > 32)
 @pytest.mark.parametrize("method", [0, 1])
 def test_random_fit(N, K, M, A, method):
     X, Y = port.synth(1000 + N + K, N, K, M, L=4)

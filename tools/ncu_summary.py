@@ -1,6 +1,8 @@
 """Summarise ncu reports (read on the CPU box) into profiles/: per-kernel launch shares and the key metrics of the
 `--set full` captures.  Usage: python tools/ncu_summary.py <round-tag> <launches.csv> <rep> [<rep> ...]"""
-import collections, csv, json, subprocess, sys
+import collections, csv, json, re, subprocess, sys
+
+PIPE = re.compile(r"pipe_tensor|tensor_op|dmma|pipe_fp64|pipe_fmaheavy.*pct|inst_executed_pipe_uniform")
 
 KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
@@ -41,6 +43,10 @@ def full(path):
         e = {"kernel": d.get("Kernel Name", "?")}
         for k in KEYS:
             if k in d:
+                e[k] = f"{d[k]} {units[hdr.index(k)]}".strip()
+        # the FP64 tensor (DMMA) sub-pipe: every tensor-pipe counter the report carries, whatever this ncu calls them
+        for k in hdr:
+            if PIPE.search(k) and k not in e and d.get(k, "") not in ("", "n/a"):
                 e[k] = f"{d[k]} {units[hdr.index(k)]}".strip()
         res.append(e)
     return res
