@@ -87,6 +87,13 @@ __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, u
                  : "memory");
 }
 
+// asynchronous bulk prefetch of a byte range into L2 (SASS UBLKPF.L2): costs no registers and no shared memory, so a
+// kernel whose occupancy is too low to hide HBM latency with loads in flight can run its streams ahead of itself.
+// addr 16-byte aligned, bytes a multiple of 16.
+__device__ __forceinline__ void l2_prefetch(const void *addr, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(addr), "r"(bytes) : "memory");
+}
+
 // Programmatic dependent launch (PDL): a kernel launched with the programmatic-stream-serialization attribute may
 // start while its predecessor in the stream is still running; pdl_wait() blocks until the predecessor grid has
 // completed and its writes are visible (a no-op without the attribute), pdl_launch() lets the successor start.

@@ -13,6 +13,7 @@
 // e_a = e_{a-1} - u q_a' : no separate prediction pass.
 // Components are extracted up to A only (the reference extracts K per fold, pls.cpp:477/531; its first A
 // are bit-identical).
+#include <chrono>
 #include <type_traits>
 #include <vector>
 
@@ -35,7 +36,11 @@ struct CvArgs {
     double *Rt;                // two-lane engine: the next r also goes here, in the tiled layout of cv_gemm.cu (or null)
     int nkt;
     double *wide;              // M > 32: per-fold scratch of wide_scratch_doubles(M) doubles (step_wide.cuh), else null
+    int prefetch;              // fused kernel: run its HBM streams ahead into L2 with bulk prefetches
+    int ring;                  // fused kernel: P_f / R_f rows arrive through a TMA-fed shared-memory ring (dynamic smem)
+    long long *trace;          // dev tool (PLSB_CV_TRACE=<component>): globaltimer ns at the fused kernel's phase boundaries
 };
+#define CV_TRACE(i) do { if (v.trace && blockIdx.x == 7 && threadIdx.x == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); v.trace[i] = t_; } } while (0)
 
 // WIDE: M > 32 responses — the M-sized objects live in a per-fold global scratch (step_wide.cuh)
 template <bool WIDE>
@@ -148,6 +153,42 @@ __device__ __forceinline__ void block_sum_vec(double (&v)[NV], double *red /* [C
     for (int i = 0; i < NV; ++i) v[i] = red[NW * NV + i];
 }
 
+// out[d] = row_d . x for ndots rows of a K-vector matrix (row d at row_of(d)), with the COLUMN-OWNER layout of the fused
+// kernel: thread t holds x at columns {t, t + NT, ...} in registers (xv), forms its share of up to NV dots at once — NV x
+// KPT independent loads in flight per thread — and the shares are summed over the CTA in a fixed order.  (One warp per
+// dot, four loads in flight per lane, left a lone fold CTA next to the product kernel with ~8 KB in flight per SM.)
+// pf_bytes > 0: rows are pf_bytes long and thread 0 keeps CV_PF of them prefetched into L2 ahead of the batch in work.
+constexpr int CV_PF = 8;
+template <int NV, typename FR>
+__device__ __forceinline__ void owner_dots(int ndots, int K, FR row_of, const double (&xv)[CV_KPT], double *out, double *red,
+                                           uint32_t pf_bytes = 0) {
+    const int tid = threadIdx.x;
+    for (int d0 = 0; d0 < ndots; d0 += NV) {
+        if (pf_bytes && tid == 0) {
+#pragma unroll
+            for (int u = 0; u < NV; ++u)
+                if (d0 + CV_PF + u < ndots) l2_prefetch(row_of(d0 + CV_PF + u), pf_bytes);
+        }
+        const double *rows[NV];
+#pragma unroll
+        for (int u = 0; u < NV; ++u) rows[u] = row_of(d0 + u < ndots ? d0 + u : ndots - 1);
+        double acc[NV];
+#pragma unroll
+        for (int u = 0; u < NV; ++u) acc[u] = 0.0;
+#pragma unroll
+        for (int j = 0; j < CV_KPT; ++j) {
+            const int k = tid + CV_FNT * j;
+            if (k < K) {
+#pragma unroll
+                for (int u = 0; u < NV; ++u) acc[u] = fma(rows[u][k], xv[j], acc[u]);
+            }
+        }
+        block_sum_vec<NV>(acc, red);
+        if (tid < NV && d0 + tid < ndots) out[d0 + tid] = acc[tid];
+    }
+    __syncthreads();
+}
+
 #ifndef PLSB_CV_MINB
 #define PLSB_CV_MINB 4
 #endif
@@ -161,11 +202,56 @@ struct FusedSmem {
     double B[2 * 64];        // work arrays of the squaring eigen solver (8 x 8 padded, two buffers)
 };
 
+// The orthogonalisation stream of the fused kernel (rows of P_f for the dots p_j'w, then rows of R_f for r -= c_j r_j:
+// 2 a K-vectors per component, 134 MB per fold at C5 — most of the kernel's traffic) through a ring of shared-memory
+// slots filled by 1-D TMA bulk copies: 64 KB in flight per CTA whatever its register budget, where plain loads keep
+// ~one row (32 KB) in flight and pay a full HBM round trip per row.  That is what makes ONE fold CTA per SM — all that
+// fits next to the product kernel of the other lane — stream at a useful rate.  No producer warp: a slot is refilled
+// by the last warp to leave it (same scheme as cv_gemm.cu).  Row a of P_f is written by this very kernel (generic
+// proxy), so its dot is taken from global memory by the threads that wrote it and it never goes through the ring.
+constexpr int CR_CH = CV_FNT * 8;                 // doubles per slot: 8 columns per thread (16 KB)
+constexpr int CR_NSLOT_MAX = 8;                   // slots are a launch parameter (CvArgs::ring = their number, default 4)
+static size_t cr_smem(int nslot) { return (size_t)nslot * CR_CH * 8 + nslot * (sizeof(uint64_t) + sizeof(int)) + 16; }
+
+struct FoldRing {
+    char *base; uint64_t *full; int *left;
+    const double *Pf, *Rf;
+    int a, nch, ldk, nP, nitems, ns; // nP: items of the P part (a rows x nch chunks); then (a + 1) rows of R; ns: slots
+    __device__ __forceinline__ void issue(int it) const {        // one thread
+        const int slot = it % ns;
+        const bool isR = it >= nP;
+        const int e = isR ? it - nP : it;
+        const int row = e / nch, ch = e % nch;
+        int cols = ldk - ch * CR_CH; cols = cols > CR_CH ? CR_CH : cols;
+        const double *src = (isR ? Rf : Pf) + (size_t)row * ldk + (size_t)ch * CR_CH;
+        mbar_arrive_expect_tx(&full[slot], (uint32_t)cols * 8u);
+        bulk_g2s(base + (size_t)slot * CR_CH * 8, src, (uint32_t)cols * 8u, &full[slot]);
+    }
+    __device__ __forceinline__ const double *acquire(int it) const {
+        const int slot = it % ns;
+        mbar_wait(&full[slot], (uint32_t)((it / ns) & 1));
+        return reinterpret_cast<const double *>(base + (size_t)slot * CR_CH * 8);
+    }
+    __device__ __forceinline__ void release(int it) const {      // all threads of the CTA, after their reads of the slot
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) {
+            const int slot = it % ns;
+            __threadfence_block();
+            if (atomicSub(&left[slot], 1) == 1) {
+                left[slot] = CV_FNT / 32;
+                __threadfence_block();
+                if (it + ns < nitems) issue(it + ns);
+            }
+        }
+    }
+};
+
 template <int MM>
-__global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT : 1) cv_fold_fused_kernel(const CvArgs v) {
+__global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT : 3) cv_fold_fused_kernel(const CvArgs v) {
+    extern __shared__ __align__(128) char cr_dyn[];
     constexpr int NP = MM * (MM + 1) / 2;
     __shared__ FusedSmem<MM> sh;
-    __shared__ double red[(CV_FNT / 32 + 1) * (NP > MM ? NP : MM)];
+    __shared__ double red[(CV_FNT / 32 + 1) * (NP > 8 ? NP : 8)];   // block_sum_vec of up to max(NPP, MM, 4) values
     __shared__ double qe[MM];
     const int tid = threadIdx.x;
     const int f = blockIdx.x;
@@ -179,10 +265,50 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
     const double *g = v.Gr + (size_t)f * ldk;
     double *pa = Pf + (size_t)a * ldk;
     double *U = v.U + (size_t)f * ts;
+    CV_TRACE(0);
 
+    // Everything this CTA is about to read for the first time comes from HBM: run those streams ahead into L2 now (one
+    // thread, a handful of bulk-prefetch instructions).  Next to the product kernel of the other lane there is ONE fold
+    // CTA per SM, and its chain of dependent phases would otherwise pay a full HBM round trip at the head of each.
+    FoldRing ring;
+    const bool use_ring = v.ring != 0 && a + 1 < v.A;     // (a CTA that returns before the stream is read must not start it)
+    if (use_ring) {
+        ring.ns = v.ring;
+        ring.base = cr_dyn;
+        ring.full = reinterpret_cast<uint64_t *>(cr_dyn + (size_t)ring.ns * CR_CH * 8);
+        ring.left = reinterpret_cast<int *>(ring.full + ring.ns);
+        ring.Pf = Pf; ring.Rf = Rf; ring.a = a; ring.ldk = ldk;
+        ring.nch = (ldk + CR_CH - 1) / CR_CH;
+        ring.nP = a * ring.nch;
+        ring.nitems = (2 * a + 1) * ring.nch;
+        if (tid == 0) {
+            for (int sl = 0; sl < ring.ns; ++sl) { mbar_init(&ring.full[sl], 1); ring.left[sl] = CV_FNT / 32; }
+            mbar_fence_init();
+            for (int it = 0; it < ring.ns && it < ring.nitems; ++it) ring.issue(it);   // rows 0.. are final: start now
+        }
+        __syncthreads();
+    }
+    const uint32_t row_bytes = (uint32_t)ldk * 8u;
+    const bool pf = v.prefetch != 0;
+    if (pf && tid == 0) {
+        l2_prefetch(r, row_bytes);
+        l2_prefetch(g, row_bytes);
+        for (int i = 0; i < ts && i < 8; ++i) l2_prefetch(v.X + h[i] * (int64_t)ldk, row_bytes);
+        for (int m = 0; m < M; ++m) l2_prefetch(Sf + (size_t)m * ldk, row_bytes);
+        for (int j = 0; j < a + 1 && j < CV_PF; ++j) l2_prefetch(Pf + (size_t)j * ldk, row_bytes);
+    }
     // ---- u = X_H r (held-out scores), then the downdate g = (X'X) r - X_H' u in registers; tt = r'g ----------------
-    warp_dots<CV_FNT>(ts, K, [&](int i) { return v.X + h[i] * (int64_t)ldk; }, [&](int) { return r; }, sh.c);
-    __syncthreads();
+    {
+        double rv[CV_KPT];
+#pragma unroll
+        for (int j = 0; j < CV_KPT; ++j) {
+            const int k = tid + CV_FNT * j;
+            rv[j] = k < K ? r[k] : 0.0;
+        }
+        if (ts == 1) owner_dots<1>(1, K, [&](int) { return v.X + h[0] * (int64_t)ldk; }, rv, sh.c, red);
+        else owner_dots<4>(ts, K, [&](int i) { return v.X + h[i] * (int64_t)ldk; }, rv, sh.c, red);
+    }
+    CV_TRACE(1);   // u done
     double gv[CV_KPT];
     double tt1[1] = {0.0};
 #pragma unroll
@@ -207,6 +333,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
     for (int i = tid; i < ts; i += CV_FNT) U[i] = sh.c[i];
     block_sum_vec<1>(tt1, red);
     const double tt = tt1[0];
+    CV_TRACE(2);   // downdate + tt done
 
     // ---- p = g / tt (stored), q = S'r / tt ---------------------------------------------------------------------------
     double qm[MM];
@@ -233,9 +360,14 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
     }
 
     // ---- S -= tt p q' fused with the Gram matrix of the deflated S ---------------------------------------------------
-    double gp[NP];
+    CV_TRACE(3);   // p, q done
+    // (MM = 8: the 36 Gram entries go in two passes of 18 accumulators — the second re-reads the thread's own columns
+    //  of the deflated S from L2 — so that the kernel fits 80 registers and three CTAs per SM, one of them next to
+    //  the product kernel of the other lane)
+    constexpr int NPASS = MM > 4 ? 2 : 1, NPP = (NP + NPASS - 1) / NPASS;
+    double gp[NPP];
 #pragma unroll
-    for (int i = 0; i < NP; ++i) gp[i] = 0.0;
+    for (int i = 0; i < NPP; ++i) gp[i] = 0.0;
 #pragma unroll
     for (int j = 0; j < CV_KPT; ++j) {
         const int k = tid + CV_FNT * j;
@@ -254,7 +386,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
 #pragma unroll
             for (int u = 0; u < MM; ++u)
 #pragma unroll
-                for (int w2 = u; w2 < MM; ++w2) { gp[pi] = fma(sv[u], sv[w2], gp[pi]); ++pi; }
+                for (int w2 = u; w2 < MM; ++w2) { if (pi < NPP) gp[pi] = fma(sv[u], sv[w2], gp[pi]); ++pi; }
         }
     }
     // residuals of the held-out rows with a+1 components: e_a = e_{a-1} - u q_a'
@@ -267,24 +399,52 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
     }
     const int an = a + 1;
     if (an >= v.A) return;
+    CV_TRACE(4);   // deflation + residuals done
 
     // ---- next weights: dominant eigenvector of S'S, w = S q / |S q| -------------------------------------------------
     if (MM > 1) {
-        block_sum_vec<NP>(gp, red);
-        if (tid == 0) {
-            int pi = 0;
 #pragma unroll
-            for (int u = 0; u < MM; ++u)
+        for (int pass = 0; pass < NPASS; ++pass) {
+            if (pass > 0) {
 #pragma unroll
-                for (int w2 = u; w2 < MM; ++w2) {
-                    if (u < M && w2 < M) { sh.gram[u * M + w2] = gp[pi]; sh.gram[w2 * M + u] = gp[pi]; }
-                    ++pi;
+                for (int i = 0; i < NPP; ++i) gp[i] = 0.0;
+#pragma unroll
+                for (int j = 0; j < CV_KPT; ++j) {
+                    const int k = tid + CV_FNT * j;
+                    if (k < K) {
+                        double sv[MM];
+#pragma unroll
+                        for (int m = 0; m < MM; ++m) sv[m] = m < M ? Sf[(size_t)m * ldk + k] : 0.0;   // written by this thread
+                        int pi = 0;
+#pragma unroll
+                        for (int u = 0; u < MM; ++u)
+#pragma unroll
+                            for (int w2 = u; w2 < MM; ++w2) {
+                                if (pi >= pass * NPP && pi < (pass + 1) * NPP) gp[pi - pass * NPP] = fma(sv[u], sv[w2], gp[pi - pass * NPP]);
+                                ++pi;
+                            }
+                    }
                 }
+            }
+            block_sum_vec<NPP>(gp, red);
+            if (tid == 0) {
+                int pi = 0;
+#pragma unroll
+                for (int u = 0; u < MM; ++u)
+#pragma unroll
+                    for (int w2 = u; w2 < MM; ++w2) {
+                        if (pi >= pass * NPP && pi < (pass + 1) * NPP && u < M && w2 < M) {
+                            sh.gram[u * M + w2] = gp[pi - pass * NPP]; sh.gram[w2 * M + u] = gp[pi - pass * NPP];
+                        }
+                        ++pi;
+                    }
+            }
         }
         __syncthreads();
         if (tid < 32) dominant_eigvec_warp<8>(sh.gram, sh.B, sh.B + 64, M, qe);
         __syncthreads();
     }
+    CV_TRACE(5);   // Gram reduced, eigenvector done
     double wv[CV_KPT];
     double n1[1] = {0.0};
 #pragma unroll
@@ -311,14 +471,62 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
         if (k < K) { wv[j] = wv[j] / nrm; w[k] = wv[j]; }
     }
     __syncthreads();
+    CV_TRACE(6);   // w normalised and stored
     // ---- r = w - sum_j (p_j'w) r_j ------------------------------------------------------------------------------------
     double *rn = Rf + (size_t)an * ldk;
+    if (use_ring) {
+        int it = 0;
+        for (int j0 = 0; j0 < a; j0 += 4) {          // c_j = p_j'w for the rows that were final when the kernel started
+            double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (j0 + u < a) {
+                    for (int ch = 0; ch < ring.nch; ++ch, ++it) {
+                        const double *sl = ring.acquire(it);
+                        if (ch == 0) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (tid + CV_FNT * j < K) acc[u] = fma(sl[tid + CV_FNT * j], wv[j], acc[u]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (CR_CH + tid + CV_FNT * j < K) acc[u] = fma(sl[tid + CV_FNT * j], wv[8 + j], acc[u]);
+                        }
+                        ring.release(it);
+                    }
+                }
+            }
+            block_sum_vec<4>(acc, red);
+            if (tid < 4 && j0 + tid < a) sh.c[j0 + tid] = acc[tid];
+        }
+        // row a = this component's p, written above by the same threads that read it back here
+        owner_dots<1>(1, K, [&](int) { return (const double *)pa; }, wv, sh.c + a, red);
+        CV_TRACE(7);   // P dots done
+        for (int jj = 0; jj < an; ++jj) {
+            const double cj = sh.c[jj];
+            for (int ch = 0; ch < ring.nch; ++ch, ++it) {
+                const double *sl = ring.acquire(it);
+                if (ch == 0) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (tid + CV_FNT * j < K) wv[j] -= cj * sl[tid + CV_FNT * j];
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (CR_CH + tid + CV_FNT * j < K) wv[8 + j] -= cj * sl[tid + CV_FNT * j];
+                }
+                ring.release(it);
+            }
+        }
+    } else
     for (int j0 = 0; j0 < an; j0 += 256) {
         const int nj = an - j0 < 256 ? an - j0 : 256;
-        warp_dots<CV_FNT>(nj, K, [&](int j) { return (const double *)(Pf + (size_t)(j0 + j) * ldk); },
-                         [&](int) { return (const double *)w; }, sh.c);
-        __syncthreads();
+        if (pf && tid == 0)
+            for (int j = 0; j < nj && j < CV_PF; ++j) l2_prefetch(Rf + (size_t)(j0 + j) * ldk, row_bytes);
+        owner_dots<4>(nj, K, [&](int j) { return (const double *)(Pf + (size_t)(j0 + j) * ldk); }, wv, sh.c, red,
+                      pf ? row_bytes : 0u);
         for (int jj = 0; jj < nj; ++jj) {   // one row of R_f: all of a thread's columns in flight at once
+            if (pf && tid == 0 && jj + CV_PF < nj) l2_prefetch(Rf + (size_t)(j0 + jj + CV_PF) * ldk, row_bytes);
             const double cj = sh.c[jj];
             const double *rr = Rf + (size_t)(j0 + jj) * ldk;
 #pragma unroll
@@ -338,6 +546,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
         }
     }
     for (int k = K + tid; k < ldk; k += CV_FNT) rn[k] = 0.0;
+    CV_TRACE(8);   // R stream done, r stored
 }
 
 struct CvBuf {
@@ -429,6 +638,15 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     }
     plsb_ctx *c = ds->ctx;
     PLSB_CUDA(cudaSetDevice(c->device));
+    const char *trace = getenv("PLSB_TRACE");
+    const auto t_start = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (trace && *trace == '1') {
+            cudaStreamSynchronize(c->stream);
+            fprintf(stderr, "[plsb] cv_folds: %s at %.3f ms\n", what,
+                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count());
+        }
+    };
     const int64_t *tloc = test_idx + fold0 * ts;
     for (int64_t i = 0; i < nfolds_local * ts; ++i)
         PLSB_ARG(tloc[i] >= 0 && tloc[i] < ds->N, "test index %lld out of range", (long long)tloc[i]);
@@ -439,11 +657,28 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     PLSB_CUDA(cudaMemcpyAsync(idx.p, tloc, (size_t)rows_local * sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
     PLSB_TRY(Ed.alloc((size_t)M * A * rows_local * 8));
 
+    lap("indices checked and queued, residual block allocated");
     auto finish = [&]() -> int {
+        lap("kernels done");
         if (press) PLSB_TRY(device_press(c, Ed.d(), rows_local, M, A, press));
-        if (E) PLSB_CUDA(cudaMemcpy2DAsync(E + fold0 * ts, (size_t)rows_total * 8, Ed.p, (size_t)rows_local * 8,
-                                           (size_t)rows_local * 8, (size_t)(M * A), cudaMemcpyDeviceToHost, c->stream));
+        if (E) {
+            // the whole residual block in one piece, bound for pageable memory: pinned staging + host threads (a plain
+            // cudaMemcpy into pageable memory runs at 2-3 GB/s: 4.3 MB of config 3 cost more than its kernel)
+            bool staged = false;
+            const size_t nE = (size_t)M * A * rows_local;
+            if (rows_local == rows_total && nE * 8 >= ((size_t)1 << 20)) {
+                cudaPointerAttributes pa{};
+                const bool pinned = cudaPointerGetAttributes(&pa, E) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+                cudaGetLastError();
+                const char *off = getenv("PLSB_NO_STAGE");
+                staged = !pinned && !(off && *off == '1');
+            }
+            if (staged) PLSB_TRY(download_staged(c, Ed.d(), nE, E, false));
+            else PLSB_CUDA(cudaMemcpy2DAsync(E + fold0 * ts, (size_t)rows_total * 8, Ed.p, (size_t)rows_local * 8,
+                                             (size_t)rows_local * 8, (size_t)(M * A), cudaMemcpyDeviceToHost, c->stream));
+        }
         PLSB_CUDA(cudaStreamSynchronize(c->stream));
+        lap("results on the host");
         return PLSB_OK;
     };
 
@@ -496,9 +731,25 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     if (const char *e = getenv("PLSB_FOLD_BATCH")) { const int64_t v = atoll(e); if (v > 0 && v < F) F = v; }
     if (F < 1 && lanes == 2) { lanes = 1; F = (int64_t)((double)free_b * 0.6 / (double)per_fold); }
     PLSB_ARG(F >= 1, "not enough device memory for one fold");
-    if (lanes == 2) {    // equal waves, an even number of them, whole GEMM column tiles (128 folds) except the last
-        const int64_t nw = 2 * ceil_div(nfolds_local, 2 * F);
-        const int64_t Fe = round_up(ceil_div(nfolds_local, nw), 128);
+    // PLSB_CVG_CTAS: run the product kernel on fewer SMs (one persistent CTA each) and leave the others entirely to the
+    // fold kernel of the other lane (three fold CTAs fit a free SM, one fits next to a product CTA).  Measured at C5
+    // (profiles/r2l_cv_ab.log): 148 / 136 / 128 / 120 / 112 product CTAs -> 1.81 / 1.76 / 1.75 / 1.82 / 1.80 s per call,
+    // i.e. no difference: the call sits at the board's power cap (1.45-1.5 GHz of 1.965), where time shifted from one
+    // stream just reappears in the other.  Default: all SMs.
+    int gemm_ctas = c->sm_count;
+    if (lanes == 2) {
+        if (const char *e = getenv("PLSB_CVG_CTAS")) { const int n = atoi(e); if (n > 0 && n <= c->sm_count) gemm_ctas = n; }
+        // equal waves, an even number of them: the count whose product items (row tiles x 128-fold column tiles) fill
+        // whole rounds of gemm_ctas CTAs best
+        const int64_t nmt = ceil_div(K, 128), nw0 = 2 * ceil_div(nfolds_local, 2 * F);
+        int64_t best_nw = nw0, best_cost = -1;
+        for (int64_t nw = nw0; nw <= nw0 + 12; nw += 2) {
+            const int64_t Fw = ceil_div(nfolds_local, nw), nnt = ceil_div(Fw, 128);
+            const int64_t cost = nw * ceil_div(nmt * nnt, gemm_ctas);
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_nw = nw; }
+            if (Fw <= 256) break;
+        }
+        const int64_t Fe = ceil_div(nfolds_local, best_nw);
         if (Fe < F) F = Fe;
     }
     if (F > nfolds_local) F = nfolds_local;
@@ -531,8 +782,9 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     v.X = ds->X; v.Y = ds->Y; v.S0 = S0full; v.test_idx = (const int64_t *)idx.p; v.E = Ed.d();
     v.rows_local = rows_local; v.K = (int)K; v.ldk = (int)ldk; v.ldm = (int)ds->ldm; v.M = (int)M; v.A = (int)A;
     v.ts = (int)ts;
+    { const char *pe = getenv("PLSB_CV_PREFETCH"); v.prefetch = pe ? atoi(pe) : 0; }   // measured: slower (profiles/r2h)
     const char *v1 = getenv("PLSB_CV_V1");   // A/B switch: the phase-by-phase kernel for every launch
-    const bool fused = K >= 1024 && K <= (int64_t)CV_KPT * CV_FNT && M <= 8 && ts <= 256 && !(v1 && *v1 == '1');
+    const bool fused = K >= 1024 && K <= (int64_t)CV_KPT * CV_FNT && M <= 8 && ts <= 256 && A <= 256 && !(v1 && *v1 == '1');
     if (lanes == 2) {
         // An SM runs with ONE shared-memory carve-out at a time: a kernel that prefers a different split of the 256 KB
         // L1/shared array than the resident product kernel (which needs the maximum) is not placed next to it.  Ask for
@@ -546,12 +798,43 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         PLSB_CUDA(cudaFuncSetAttribute(cv_fold_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
         PLSB_CUDA(cudaFuncSetAttribute(cv_fold_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     }
+    {   // the TMA-fed ring for the orthogonalisation stream
+        const char *re = getenv("PLSB_CV_RING");
+        int ns = 4;                                   // PLSB_CV_RING = 0 (plain loads) or the number of 16 KB slots
+        if (re) { ns = atoi(re); if (ns == 1) ns = 4; if (ns > CR_NSLOT_MAX) ns = CR_NSLOT_MAX; if (ns < 0) ns = 0; }
+        v.ring = fused ? ns : 0;
+        if (v.ring) {
+            const int fsm_max = (int)cr_smem(CR_NSLOT_MAX);
+            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
+            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
+            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
+            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
+        }
+    }
+    const size_t fsm = v.ring ? cr_smem(v.ring) : 0;
+    CvBuf tracebuf(c);
+    int trace_a = -1, traced = 0;
+    if (const char *te = getenv("PLSB_CV_TRACE")) {
+        trace_a = atoi(te);
+        PLSB_TRY(tracebuf.alloc(16 * sizeof(long long)));
+        PLSB_CUDA(cudaMemsetAsync(tracebuf.p, 0, 16 * sizeof(long long), c->stream));
+    }
+    auto dump_trace = [&]() {
+        if (!tracebuf.p) return;
+        long long hh[16];
+        cudaStreamSynchronize(c->stream);
+        if (cudaMemcpy(hh, tracebuf.p, sizeof(hh), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+        fprintf(stderr, "[plsb] fused fold kernel, component %d, CTA 7, ns since its start:", trace_a);
+        for (int i = 1; i <= 8; ++i) fprintf(stderr, " %lld", hh[i] ? hh[i] - hh[0] : -1);
+        fprintf(stderr, "  (u | downdate+tt | p,q | deflate | gram+eig | w | P dots | R stream)\n");
+    };
     auto launch_fold = [&](cudaStream_t st, int a, int nf) -> int {
+        v.trace = (a == trace_a && a >= 0 && traced++ == 1) ? (long long *)tracebuf.p : nullptr;   // the second wave's launch
         if (a >= 0 && fused) {
-            if (M == 1) cv_fold_fused_kernel<1><<<nf, CV_FNT, 0, st>>>(v);
-            else if (M == 2) cv_fold_fused_kernel<2><<<nf, CV_FNT, 0, st>>>(v);
-            else if (M <= 4) cv_fold_fused_kernel<4><<<nf, CV_FNT, 0, st>>>(v);
-            else cv_fold_fused_kernel<8><<<nf, CV_FNT, 0, st>>>(v);
+            if (M == 1) cv_fold_fused_kernel<1><<<nf, CV_FNT, fsm, st>>>(v);
+            else if (M == 2) cv_fold_fused_kernel<2><<<nf, CV_FNT, fsm, st>>>(v);
+            else if (M <= 4) cv_fold_fused_kernel<4><<<nf, CV_FNT, fsm, st>>>(v);
+            else cv_fold_fused_kernel<8><<<nf, CV_FNT, fsm, st>>>(v);
         } else if (M > PLSB_MAX_M) {
             cv_fold_kernel<true><<<nf, CV_NT, 0, st>>>(v);
         } else {
@@ -580,7 +863,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
                 PLSB_TRY(launch_fold(c->stream, a, nf));
             }
         }
-        return finish();
+        { dump_trace(); return finish(); }
     }
 
     // ---- two lanes ----------------------------------------------------------------------------------------------
@@ -615,6 +898,9 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
             PLSB_CUDA(cudaEventCreateWithFlags(&ln[l]->evF, cudaEventDisableTiming));
         }
     }
+    // the product kernel's ring depth: 2 stages (141 KB) next to a fold kernel that brings its own 64 KB ring, else 3
+    int gemm_stages = v.ring ? 2 : 3;
+    if (const char *e = getenv("PLSB_CVG_STAGES")) { const int n = atoi(e); if (n == 2 || n == 3) gemm_stages = n; }
     // everything queued so far (allocations, index upload, the cross products) happens before the lanes start
     PLSB_CUDA(cudaEventRecord(sx.e0, c->stream));
     PLSB_CUDA(cudaStreamWaitEvent(sx.g, sx.e0, 0));
@@ -635,7 +921,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
                     PLSB_CUDA(cudaStreamWaitEvent(sx.g, L.evF, 0));            // r_a of this lane is ready
                     {
                         ProfScope ps(c, PLSB_PROF_CV_GEMM, sx.g);
-                        PLSB_TRY(launch_cv_gemm(c, sx.g, Gt.d(), L.Rt.d(), K, ldk, nfl[l], L.Gr.d()));
+                        PLSB_TRY(launch_cv_gemm(c, sx.g, Gt.d(), L.Rt.d(), K, ldk, nfl[l], L.Gr.d(), gemm_stages, gemm_ctas));
                     }
                     PLSB_CUDA(cudaEventRecord(L.evG, sx.g));
                     PLSB_CUDA(cudaStreamWaitEvent(sx.f, L.evG, 0));
@@ -653,7 +939,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     PLSB_CUDA(cudaEventRecord(sx.e1, sx.f));
     PLSB_CUDA(cudaStreamWaitEvent(c->stream, sx.e0, 0));
     PLSB_CUDA(cudaStreamWaitEvent(c->stream, sx.e1, 0));
-    return finish();
+    { dump_trace(); return finish(); }
 }
 
 extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,

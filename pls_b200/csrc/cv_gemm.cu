@@ -22,7 +22,7 @@
 
 namespace plsb {
 
-constexpr int CG_BM = 128, CG_BN = 128, CG_BK = 32, CG_LDA = 132, CG_LDB = 36, CG_STAGES = 3, CG_CW = 8;
+constexpr int CG_BM = 128, CG_BN = 128, CG_BK = 32, CG_LDA = 132, CG_LDB = 36, CG_CW = 8;
 constexpr int CG_A_BYTES = CG_BK * CG_LDA * 8;      // 33 792
 constexpr int CG_B_BYTES = CG_BN * CG_LDB * 8;      // 36 864
 constexpr int CG_STAGE = CG_A_BYTES + CG_B_BYTES;
@@ -56,6 +56,8 @@ __device__ __forceinline__ void cg_dmma(double &c0, double &c1, double a, double
                  : "d"(a), "d"(b));
 }
 
+// CG_STAGES: 3 (212 KB of shared memory), or 2 (141 KB) when the fold kernel of the other lane brings its own 64 KB ring
+template <int CG_STAGES>
 __global__ void __maxnreg__(168) cv_gemm_kernel(const CvGemmArgs g) {
     extern __shared__ __align__(128) char smem[];
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)CG_STAGES * CG_STAGE);
@@ -143,15 +145,19 @@ int launch_cv_gemm_tile_g(plsb_ctx *c, cudaStream_t st, const double *G, int64_t
     return PLSB_OK;
 }
 
-int launch_cv_gemm(plsb_ctx *c, cudaStream_t st, const double *Gt, const double *Rt, int64_t K, int64_t ldk, int nf, double *Gr) {
+int launch_cv_gemm(plsb_ctx *c, cudaStream_t st, const double *Gt, const double *Rt, int64_t K, int64_t ldk, int nf, double *Gr,
+                   int stages, int max_ctas) {
     CvGemmArgs g{};
     g.Gt = Gt; g.Rt = Rt; g.Gr = Gr; g.K = (int)K; g.ldk = (int)ldk; g.nf = nf;
     g.nkt = (int)ceil_div(K, CG_BK); g.nmt = (int)ceil_div(K, CG_BM); g.nnt = (int)ceil_div(nf, CG_BN);
-    const size_t smem = (size_t)CG_STAGES * CG_STAGE + CG_STAGES * sizeof(uint64_t) + CG_STAGES * sizeof(int) + 16;
-    PLSB_CUDA(cudaFuncSetAttribute(cv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int ns = stages == 2 ? 2 : 3;
+    const size_t smem = (size_t)ns * CG_STAGE + ns * sizeof(uint64_t) + ns * sizeof(int) + 16;
+    auto kern = ns == 2 ? cv_gemm_kernel<2> : cv_gemm_kernel<3>;
+    PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int nitems = g.nmt * g.nnt;
-    const int grid = nitems < c->sm_count ? nitems : c->sm_count;
-    cv_gemm_kernel<<<grid, CG_CW * 32, smem, st>>>(g);
+    int grid = nitems < c->sm_count ? nitems : c->sm_count;
+    if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;     // SMs left entirely to the other lane's fold kernel (cv.cu)
+    kern<<<grid, CG_CW * 32, smem, st>>>(g);
     c->launches++;
     PLSB_CUDA(cudaGetLastError());
     return PLSB_OK;

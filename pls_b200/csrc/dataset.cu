@@ -65,6 +65,11 @@ int download_staged(plsb_ctx *c, const double *dev, size_t n, double *host, bool
             }
         });
     };
+    const char *trace = getenv("PLSB_TRACE");
+    const bool tr = trace && *trace == '1';
+    const auto t0 = std::chrono::steady_clock::now();
+    double wait_s = 0, move_s = 0;
+    auto now_s = [&] { return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count(); };
     for (size_t i = 0; i < nch; ++i) {
         const size_t off = i * per, cnt = n - off < per ? n - off : per;
         PLSB_CUDA(cudaMemcpyAsync(h.dbuf[i & 1], dev + off, cnt * 8, cudaMemcpyDeviceToHost, c->copy_stream));
@@ -74,8 +79,13 @@ int download_staged(plsb_ctx *c, const double *dev, size_t n, double *host, bool
             move_out(i - 1);
         }
     }
+    const double ta = now_s();
     PLSB_CUDA(cudaEventSynchronize(h.ddone[(nch - 1) & 1]));
+    const double tb = now_s();
     move_out(nch - 1);
+    wait_s = tb - ta; move_s = now_s() - tb;
+    if (tr) fprintf(stderr, "[plsb] staged download of %.1f MB: %.3f ms in all; last chunk: %.3f ms waiting for the copy, %.3f ms moving it out\n",
+                    n * 8e-6, now_s() * 1e3, wait_s * 1e3, move_s * 1e3);
     return PLSB_OK;
 }
 
