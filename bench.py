@@ -133,13 +133,24 @@ def small_cv_legs(ctx, with_cpu=True, as_built=False):
         reps = 20
         ctx.sync(); t0 = time.perf_counter()
         for _ in range(reps):
-            E = ds.cv_folds(10, 0, te)
+            E = ds.cv_folds(10, 0, te)                 # a fresh residual block per call (what Model::cv_* returns)
+        ctx.sync(); sec_fresh = (time.perf_counter() - t0) / reps
+        Eout = np.zeros((Y.shape[1], 10, te.size))
+        ds.cv_folds(10, 0, te, out=Eout)
+        ctx.sync(); t0 = time.perf_counter()
+        for _ in range(reps):
+            E = ds.cv_folds(10, 0, te, out=Eout)       # the caller's block reused (no first-touch page faults in the copy)
         ctx.sync(); sec = (time.perf_counter() - t0) / reps
+        ctx.sync(); t0 = time.perf_counter()
+        for _ in range(reps):
+            ds.cv_press(10, 0, te)                     # validation's sums only: the block never leaves the device
+        ctx.sync(); sec_press = (time.perf_counter() - t0) / reps
         press = (E.reshape(Y.shape[1], -1, 10) ** 2).sum(axis=1)
         want = g[key + "_ress"] if (key + "_ress") in g.files else None
         err = float(np.abs(press - want).max() / np.abs(want).max()) if want is not None else None
         out[name] = {"folds": int(te.shape[0]), "held_out_rows": int(te.shape[1]), "fits_per_s": te.shape[0] / sec,
-                     "ms_per_call": sec * 1e3, "press_rel_err_vs_reference": err}
+                     "ms_per_call": sec * 1e3, "ms_per_call_fresh_output_block": sec_fresh * 1e3,
+                     "ms_per_call_press_only": sec_press * 1e3, "press_rel_err_vs_reference": err}
         ds.close()
         out[name]["_data"] = (X, Y, te, g, key, E)
     for name in list(out):
@@ -484,10 +495,14 @@ def run_ours(args):
         f0, f1 = sharding.fold_shard(n5, rank, world)
         E = np.zeros((m5, a5, n5))
         ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)   # warm-up: the whole call (buffers, both lanes)
-        # (1) the timed call: two lanes in flight, no event between kernels
-        ctx.profile(False)
+        # (1) the timed call: X'X and X'Y once (each rank reads its row slice, partial matrices all-reduced), then the
+        # folds of this rank — two lanes in flight, no event between kernels
+        ctx.profile(3); ctx.profile_reset()
         barrier()
         t0 = time.perf_counter()
+        ds5.build_gram(across_ranks=world > 1)
+        xtx_ms, _ = ctx.profile_get("xtx")
+        ctx.profile(False)
         ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)              # includes D2H of the residual block
         barrier()
         cv_s = time.perf_counter() - t0
@@ -497,7 +512,7 @@ def run_ours(args):
         ds5.cv_folds(a5, 0, te, fold0=f0, nfolds_local=f1 - f0, out=E)
         barrier()
         cv_instr_s = time.perf_counter() - t1
-        gemm_ov, ngemm = ctx.profile_get("cv_gemm"); fold_ov, _ = ctx.profile_get("cv_fold"); xtx_ms, _ = ctx.profile_get("xtx")
+        gemm_ov, ngemm = ctx.profile_get("cv_gemm"); fold_ov, _ = ctx.profile_get("cv_fold")
         # (3) the same kernels and buffers one after the other (PLSB_CV_SERIAL): each kernel alone on the GPU — the
         # product kernel's FP64 tensor roofline, the fold kernels' HBM time
         ctx.profile_reset()

@@ -301,6 +301,16 @@ def fitted(ctx, R, Q, comp, Xn, Yn=None):
     return out
 
 
+def sse(ctx, R, Q, comp, Xn, Yn):
+    """Model::SSE (pls.cpp:457-459): column sums of squared residuals with `comp` components, reduced on the device"""
+    R, Q, Xn, Yn = F(R), F(Q), F(Xn), F(Yn)
+    Nn = Xn.shape[0]
+    out = np.zeros(Q.shape[0])
+    check(lib().plsb_sse(ctx.h, P(R), P(Q), i64(R.shape[0]), i64(Q.shape[0]), i64(comp), P(Xn), i64(max(Nn, 1)), i64(Nn),
+                         P(Yn), i64(max(Nn, 1)), P(out)))
+    return out
+
+
 def predict_residuals(ctx, R, Q, Xn, Yn):
     R, Q, Xn, Yn = F(R), F(Q), F(Xn), F(Yn)
     K, A = R.shape

@@ -101,12 +101,11 @@ class Model:
         return _capi.fitted(self.ctx, self.R, self.Q, self._comp(comp), X, Y)
 
     def SSE(self, X, Y, comp=None):
-        e = self.residuals(X, Y, comp)
-        return (e * e).sum(axis=0)
+        return _capi.sse(self.ctx, self.R, self.Q, self._comp(comp), X, Y)          # plsb_sse (pls.cpp:457-459)
 
     def explained_variance(self, X, Y, comp=None):
         Y = _capi.F(Y)
-        sst = ((Y - Y.mean(axis=0)) ** 2).sum(axis=0) if Y.shape[0] >= 2 else np.zeros(Y.shape[1])
+        sst = _capi.colstats(self.ctx, Y)[1] if Y.shape[0] >= 2 else np.zeros(Y.shape[1])   # SST on the device (pls.cpp:69-77)
         return 1.0 - self.SSE(X, Y, comp) / sst
 
     # -- cross-validation --------------------------------------------------------------------------
