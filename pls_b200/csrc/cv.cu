@@ -617,7 +617,7 @@ static int device_press(plsb_ctx *c, const double *Ed, int64_t rows, int64_t M, 
 // small-data regime (cv_small.cu)
 bool cv_small_supported(const plsb_ctx *c, const plsb_dataset *ds, int64_t A, int64_t ts, bool *pr_in_smem);
 int launch_cv_small(plsb_ctx *c, const plsb_dataset *ds, int64_t A, const int64_t *idx_dev, int64_t nf, int64_t ts,
-                    int64_t rows_local, double *Ed, bool pr_in_smem);
+                    int64_t rows_local, double *Ed, bool pr_in_smem, int64_t nf_total);
 
 }  // namespace plsb
 
@@ -687,7 +687,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         bool pr_in_smem = false;
         const char *off = getenv("PLSB_CV_NO_SMALL");
         if (!(off && *off == '1') && cv_small_supported(c, ds, A, ts, &pr_in_smem)) {
-            PLSB_TRY(launch_cv_small(c, ds, A, (const int64_t *)idx.p, nfolds_local, ts, rows_local, Ed.d(), pr_in_smem));
+            PLSB_TRY(launch_cv_small(c, ds, A, (const int64_t *)idx.p, nfolds_local, ts, rows_local, Ed.d(), pr_in_smem, nfolds_total));
             return finish();
         }
     }
@@ -719,15 +719,15 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     int lanes = 2;
     if (const char *e = getenv("PLSB_CV_LANES")) { const int l = atoi(e); if (l == 1 || l == 2) lanes = l; }
     if (c->prof == 1 || nfolds_local < 512) lanes = 1;
-    // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles.  At most 4736
-    // folds = 37 column tiles of the batched GEMM: with K = 4096 (32 row tiles) that is 1184 CTAs = 8 full waves of
-    // 148 SMs, with K = 2048 four.
+    // wave size from free memory: per fold S (M), P and R (A each), w, Gr: (M + 2A + 2) * ldk doubles.  One lane: at most
+    // 4736 folds = 37 column tiles of the batched GEMM (with K = 4096, 32 row tiles, that is 1184 CTAs = 8 full waves of
+    // 148 SMs, with K = 2048 four).  Two lanes: at most 6144 per wave; the wave count is chosen below.
     size_t free_b = 0;
     PLSB_TRY(dev_mem_available(c, &free_b));
     const size_t per_fold = (size_t)(M + 2 * A + 2) * ldk * 8 + (size_t)ts * 8 + (lanes == 2 ? (size_t)ldk * 9 + 64 : 0) +
                             step_wide_scratch_bytes((int)M);
     int64_t F = (int64_t)((double)free_b * 0.6 / (double)per_fold) / lanes;
-    if (F > 4736) F = 4736;
+    if (F > (lanes == 2 ? 6144 : 4736)) F = lanes == 2 ? 6144 : 4736;
     if (const char *e = getenv("PLSB_FOLD_BATCH")) { const int64_t v = atoll(e); if (v > 0 && v < F) F = v; }
     if (F < 1 && lanes == 2) { lanes = 1; F = (int64_t)((double)free_b * 0.6 / (double)per_fold); }
     PLSB_ARG(F >= 1, "not enough device memory for one fold");
@@ -743,7 +743,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         // whole rounds of gemm_ctas CTAs best
         const int64_t nmt = ceil_div(K, 128), nw0 = 2 * ceil_div(nfolds_local, 2 * F);
         int64_t best_nw = nw0, best_cost = -1;
-        for (int64_t nw = nw0; nw <= nw0 + 12; nw += 2) {
+        for (int64_t nw = nw0; nw <= (4 * nw0 > nw0 + 12 ? 4 * nw0 : nw0 + 12); nw += 2) {
             const int64_t Fw = ceil_div(nfolds_local, nw), nnt = ceil_div(Fw, 128);
             const int64_t cost = nw * ceil_div(nmt * nnt, gemm_ctas);
             if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_nw = nw; }

@@ -420,7 +420,7 @@ bool cv_small_supported(const plsb_ctx *c, const plsb_dataset *ds, int64_t A, in
 
 // folds [0, nf) of idx_dev (local numbering) -> Ed (columns of rows_local entries)
 int launch_cv_small(plsb_ctx *c, const plsb_dataset *ds, int64_t A, const int64_t *idx_dev, int64_t nf, int64_t ts,
-                    int64_t rows_local, double *Ed, bool pr_in_smem) {
+                    int64_t rows_local, double *Ed, bool pr_in_smem, int64_t nf_total) {
     CvSmallArgs v{};
     v.X = ds->X; v.Y = ds->Y; v.test_idx = idx_dev; v.E = Ed; v.rows_local = rows_local;
     v.N = (int)ds->N; v.K = (int)ds->K; v.ldk = (int)ds->ldk; v.ldm = (int)ds->ldm; v.M = (int)ds->M; v.A = (int)A;
@@ -428,7 +428,9 @@ int launch_cv_small(plsb_ctx *c, const plsb_dataset *ds, int64_t A, const int64_
     const int grid = (int)(nf < c->sm_count ? nf : c->sm_count);
     // more folds than SMs: a warp per fold, eight folds in flight per SM; otherwise a whole CTA per fold finishes sooner
     // (C2 LOO, 60 folds: 0.10 ms against 0.20 ms)
-    if (nf > c->sm_count && cv_warp_supported(c, ds, A, ts)) {
+    // The choice goes by the TOTAL fold count of the cross-validation, not by this call's share of it: the two kernels
+    // sum in different orders, and fold shards on several GPUs must reproduce the single-GPU residuals bit for bit.
+    if (nf_total > c->sm_count && cv_warp_supported(c, ds, A, ts)) {
         const size_t smem = cv_warp_layout(v.N, v.ldk, v.ldm, v.M, v.ts).total;
         switch (v.M) {
             case 1: return launch_cv_warp_m<1>(c, v, smem, grid);
