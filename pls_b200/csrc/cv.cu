@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
 #define PLSB_CV_FNT 256
 #endif
 constexpr int CV_FNT = PLSB_CV_FNT;          // threads of the fused kernel
-constexpr int CV_KPT = 4096 / CV_FNT;        // columns per thread: K <= 4096
+constexpr int CV_KPT_MAX = 4096 / CV_FNT;    // columns per thread: 16 (K <= 4096) or, as a template parameter, 8 (K <= 2048)
 
 // sums NV per-thread values over the CTA; every thread receives all NV totals (fixed order: deterministic)
 template <int NV>
@@ -159,8 +159,8 @@ __device__ __forceinline__ void block_sum_vec(double (&v)[NV], double *red /* [C
 // dot, four loads in flight per lane, left a lone fold CTA next to the product kernel with ~8 KB in flight per SM.)
 // pf_bytes > 0: rows are pf_bytes long and thread 0 keeps CV_PF of them prefetched into L2 ahead of the batch in work.
 constexpr int CV_PF = 8;
-template <int NV, typename FR>
-__device__ __forceinline__ void owner_dots(int ndots, int K, FR row_of, const double (&xv)[CV_KPT], double *out, double *red,
+template <int NV, int KPT, typename FR>
+__device__ __forceinline__ void owner_dots(int ndots, int K, FR row_of, const double (&xv)[KPT], double *out, double *red,
                                            uint32_t pf_bytes = 0) {
     const int tid = threadIdx.x;
     for (int d0 = 0; d0 < ndots; d0 += NV) {
@@ -176,7 +176,7 @@ __device__ __forceinline__ void owner_dots(int ndots, int K, FR row_of, const do
 #pragma unroll
         for (int u = 0; u < NV; ++u) acc[u] = 0.0;
 #pragma unroll
-        for (int j = 0; j < CV_KPT; ++j) {
+        for (int j = 0; j < KPT; ++j) {
             const int k = tid + CV_FNT * j;
             if (k < K) {
 #pragma unroll
@@ -246,8 +246,12 @@ struct FoldRing {
     }
 };
 
-template <int MM>
-__global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT : 3) cv_fold_fused_kernel(const CvArgs v) {
+// KPT = columns per thread: 16 covers K <= 4096; 8 (K <= 2048) halves the register arrays, so that the M = 8 variant fits
+// 64 registers as well and four CTAs share an SM instead of three (a CTA's life is a chain of dependent phases: its
+// throughput is the number of CTAs in flight)
+template <int MM, int KPT, int MINB = (MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT : 3)>
+__global__ void __launch_bounds__(CV_FNT, MINB) cv_fold_fused_kernel(const CvArgs v) {
+    constexpr int CV_KPT = KPT;
     extern __shared__ __align__(128) char cr_dyn[];
     constexpr int NP = MM * (MM + 1) / 2;
     __shared__ FusedSmem<MM> sh;
@@ -305,8 +309,8 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
             const int k = tid + CV_FNT * j;
             rv[j] = k < K ? r[k] : 0.0;
         }
-        if (ts == 1) owner_dots<1>(1, K, [&](int) { return v.X + h[0] * (int64_t)ldk; }, rv, sh.c, red);
-        else owner_dots<4>(ts, K, [&](int i) { return v.X + h[i] * (int64_t)ldk; }, rv, sh.c, red);
+        if (ts == 1) owner_dots<1, KPT>(1, K, [&](int) { return v.X + h[0] * (int64_t)ldk; }, rv, sh.c, red);
+        else owner_dots<4, KPT>(ts, K, [&](int i) { return v.X + h[i] * (int64_t)ldk; }, rv, sh.c, red);
     }
     CV_TRACE(1);   // u done
     double gv[CV_KPT];
@@ -487,7 +491,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
 #pragma unroll
                             for (int j = 0; j < 8; ++j)
                                 if (tid + CV_FNT * j < K) acc[u] = fma(sl[tid + CV_FNT * j], wv[j], acc[u]);
-                        } else {
+                        } else if constexpr (KPT > 8) {
 #pragma unroll
                             for (int j = 0; j < 8; ++j)
                                 if (CR_CH + tid + CV_FNT * j < K) acc[u] = fma(sl[tid + CV_FNT * j], wv[8 + j], acc[u]);
@@ -500,7 +504,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
             if (tid < 4 && j0 + tid < a) sh.c[j0 + tid] = acc[tid];
         }
         // row a = this component's p, written above by the same threads that read it back here
-        owner_dots<1>(1, K, [&](int) { return (const double *)pa; }, wv, sh.c + a, red);
+        owner_dots<1, KPT>(1, K, [&](int) { return (const double *)pa; }, wv, sh.c + a, red);
         CV_TRACE(7);   // P dots done
         for (int jj = 0; jj < an; ++jj) {
             const double cj = sh.c[jj];
@@ -510,7 +514,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         if (tid + CV_FNT * j < K) wv[j] -= cj * sl[tid + CV_FNT * j];
-                } else {
+                } else if constexpr (KPT > 8) {
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         if (CR_CH + tid + CV_FNT * j < K) wv[8 + j] -= cj * sl[tid + CV_FNT * j];
@@ -523,7 +527,7 @@ __global__ void __launch_bounds__(CV_FNT, MM <= 4 ? PLSB_CV_MINB * 256 / CV_FNT 
         const int nj = an - j0 < 256 ? an - j0 : 256;
         if (pf && tid == 0)
             for (int j = 0; j < nj && j < CV_PF; ++j) l2_prefetch(Rf + (size_t)(j0 + j) * ldk, row_bytes);
-        owner_dots<4>(nj, K, [&](int j) { return (const double *)(Pf + (size_t)(j0 + j) * ldk); }, wv, sh.c, red,
+        owner_dots<4, KPT>(nj, K, [&](int j) { return (const double *)(Pf + (size_t)(j0 + j) * ldk); }, wv, sh.c, red,
                       pf ? row_bytes : 0u);
         for (int jj = 0; jj < nj; ++jj) {   // one row of R_f: all of a thread's columns in flight at once
             if (pf && tid == 0 && jj + CV_PF < nj) l2_prefetch(Rf + (size_t)(j0 + jj + CV_PF) * ldk, row_bytes);
@@ -784,31 +788,36 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     v.ts = (int)ts;
     { const char *pe = getenv("PLSB_CV_PREFETCH"); v.prefetch = pe ? atoi(pe) : 0; }   // measured: slower (profiles/r2h)
     const char *v1 = getenv("PLSB_CV_V1");   // A/B switch: the phase-by-phase kernel for every launch
-    const bool fused = K >= 1024 && K <= (int64_t)CV_KPT * CV_FNT && M <= 8 && ts <= 256 && A <= 256 && !(v1 && *v1 == '1');
+    const bool fused = K >= 1024 && K <= (int64_t)CV_KPT_MAX * CV_FNT && M <= 8 && ts <= 256 && A <= 256 && !(v1 && *v1 == '1');
+    // the instance of the fused kernel for this shape: responses 1 / 2 / <= 4 / <= 8, columns per thread 8 (K <= 2048) / 16
+    void (*fused_kern)(const CvArgs) = nullptr;
+    const bool kpt8 = ldk <= 8 * CV_FNT;
+    if (M == 1) fused_kern = kpt8 ? cv_fold_fused_kernel<1, 8> : cv_fold_fused_kernel<1, 16>;
+    else if (M == 2) fused_kern = kpt8 ? cv_fold_fused_kernel<2, 8> : cv_fold_fused_kernel<2, 16>;
+    else if (M <= 4) fused_kern = kpt8 ? cv_fold_fused_kernel<4, 8> : cv_fold_fused_kernel<4, 16>;
+    else {
+        const char *mb = getenv("PLSB_CV_M8_MINB");      // A/B: four CTAs per SM at 64 registers (spills) or three at 80
+        fused_kern = kpt8 ? ((mb && *mb == '4') ? cv_fold_fused_kernel<8, 8, 4> : cv_fold_fused_kernel<8, 8, 3>) : cv_fold_fused_kernel<8, 16>;
+    }
     if (lanes == 2) {
         // An SM runs with ONE shared-memory carve-out at a time: a kernel that prefers a different split of the 256 KB
         // L1/shared array than the resident product kernel (which needs the maximum) is not placed next to it.  Ask for
         // the same carve-out for the fold kernels, so that they can share the SMs.  (PLSB_CV_CARVEOUT=0: A/B)
         const char *ce = getenv("PLSB_CV_CARVEOUT");
         const int carve = (ce && *ce == '0') ? cudaSharedmemCarveoutDefault : cudaSharedmemCarveoutMaxShared;
-        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
-        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
-        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<4>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
-        PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<8>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        PLSB_CUDA(cudaFuncSetAttribute(fused_kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
         PLSB_CUDA(cudaFuncSetAttribute(cv_fold_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
         PLSB_CUDA(cudaFuncSetAttribute(cv_fold_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     }
     {   // the TMA-fed ring for the orthogonalisation stream
         const char *re = getenv("PLSB_CV_RING");
-        int ns = 4;                                   // PLSB_CV_RING = 0 (plain loads) or the number of 16 KB slots
-        if (re) { ns = atoi(re); if (ns == 1) ns = 4; if (ns > CR_NSLOT_MAX) ns = CR_NSLOT_MAX; if (ns < 0) ns = 0; }
+        int ns = kpt8 ? 3 : 4;                        // PLSB_CV_RING = 0 (plain loads) or the number of 16 KB slots
+                                                      // (K <= 2048: a slot is a whole row; 3 slots let four CTAs share an SM)
+        if (re) { ns = atoi(re); if (ns == 1) ns = kpt8 ? 3 : 4; if (ns > CR_NSLOT_MAX) ns = CR_NSLOT_MAX; if (ns < 0) ns = 0; }
         v.ring = fused ? ns : 0;
         if (v.ring) {
             const int fsm_max = (int)cr_smem(CR_NSLOT_MAX);
-            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
-            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
-            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
-            PLSB_CUDA(cudaFuncSetAttribute(cv_fold_fused_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
+            PLSB_CUDA(cudaFuncSetAttribute(fused_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));
         }
     }
     const size_t fsm = v.ring ? cr_smem(v.ring) : 0;
@@ -831,10 +840,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     auto launch_fold = [&](cudaStream_t st, int a, int nf) -> int {
         v.trace = (a == trace_a && a >= 0 && traced++ == 1) ? (long long *)tracebuf.p : nullptr;   // the second wave's launch
         if (a >= 0 && fused) {
-            if (M == 1) cv_fold_fused_kernel<1><<<nf, CV_FNT, fsm, st>>>(v);
-            else if (M == 2) cv_fold_fused_kernel<2><<<nf, CV_FNT, fsm, st>>>(v);
-            else if (M <= 4) cv_fold_fused_kernel<4><<<nf, CV_FNT, fsm, st>>>(v);
-            else cv_fold_fused_kernel<8><<<nf, CV_FNT, fsm, st>>>(v);
+            fused_kern<<<nf, CV_FNT, fsm, st>>>(v);
         } else if (M > PLSB_MAX_M) {
             cv_fold_kernel<true><<<nf, CV_NT, 0, st>>>(v);
         } else {
