@@ -39,7 +39,16 @@ struct CvArgs {
     int prefetch;              // fused kernel: run its HBM streams ahead into L2 with bulk prefetches
     int ring;                  // fused kernel: P_f / R_f rows arrive through a TMA-fed shared-memory ring (dynamic smem)
     long long *trace;          // dev tool (PLSB_CV_TRACE=<component>): globaltimer ns at the fused kernel's phase boundaries
+    long long *cta_trace;      // dev tool (PLSB_CV_CTA_TRACE=<component>): per CTA (smid, start ns, end ns) of one launch
+    unsigned long long *span;  // dev tool (PLSB_CV_TIMELINE=1): [2] = earliest CTA start / latest CTA end of THIS launch (ns)
 };
+__device__ __forceinline__ void cv_span_mark(unsigned long long *span, int which) {
+    if (span && threadIdx.x == 0) {
+        unsigned long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        if (which == 0) atomicMin(span, t_); else atomicMax(span + 1, t_);
+    }
+}
 #define CV_TRACE(i) do { if (v.trace && blockIdx.x == 7 && threadIdx.x == 0) { long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); v.trace[i] = t_; } } while (0)
 
 // WIDE: M > 32 responses — the M-sized objects live in a per-fold global scratch (step_wide.cuh)
@@ -269,7 +278,14 @@ __global__ void __launch_bounds__(CV_FNT, MINB) cv_fold_fused_kernel(const CvArg
     const double *g = v.Gr + (size_t)f * ldk;
     double *pa = Pf + (size_t)a * ldk;
     double *U = v.U + (size_t)f * ts;
+    cv_span_mark(v.span, 0);
     CV_TRACE(0);
+    if (v.cta_trace && tid == 0) {
+        unsigned smid; long long t_;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        v.cta_trace[3 * (size_t)f] = smid; v.cta_trace[3 * (size_t)f + 1] = t_;
+    }
 
     // Everything this CTA is about to read for the first time comes from HBM: run those streams ahead into L2 now (one
     // thread, a handful of bulk-prefetch instructions).  Next to the product kernel of the other lane there is ONE fold
@@ -402,7 +418,7 @@ __global__ void __launch_bounds__(CV_FNT, MINB) cv_fold_fused_kernel(const CvArg
         v.E[((size_t)m * v.A + a) * v.rows_local + row] = prev - sh.c[i] * sh.q[m];
     }
     const int an = a + 1;
-    if (an >= v.A) return;
+    if (an >= v.A) { cv_span_mark(v.span, 1); return; }
     CV_TRACE(4);   // deflation + residuals done
 
     // ---- next weights: dominant eigenvector of S'S, w = S q / |S q| -------------------------------------------------
@@ -551,6 +567,12 @@ __global__ void __launch_bounds__(CV_FNT, MINB) cv_fold_fused_kernel(const CvArg
     }
     for (int k = K + tid; k < ldk; k += CV_FNT) rn[k] = 0.0;
     CV_TRACE(8);   // R stream done, r stored
+    cv_span_mark(v.span, 1);
+    if (v.cta_trace && tid == 0) {
+        long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        v.cta_trace[3 * (size_t)f + 2] = t_;
+    }
 }
 
 struct CvBuf {
@@ -738,8 +760,8 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     // PLSB_CVG_CTAS: run the product kernel on fewer SMs (one persistent CTA each) and leave the others entirely to the
     // fold kernel of the other lane (three fold CTAs fit a free SM, one fits next to a product CTA).  Measured at C5
     // (profiles/r2l_cv_ab.log): 148 / 136 / 128 / 120 / 112 product CTAs -> 1.81 / 1.76 / 1.75 / 1.82 / 1.80 s per call,
-    // i.e. no difference: the call sits at the board's power cap (1.45-1.5 GHz of 1.965), where time shifted from one
-    // stream just reappears in the other.  Default: all SMs.
+    // i.e. no difference — what the slot model of DESIGN 3.6 predicts: product slots and fold slots trade one for one
+    // along the same line.  Default: all SMs.
     int gemm_ctas = c->sm_count;
     if (lanes == 2) {
         if (const char *e = getenv("PLSB_CVG_CTAS")) { const int n = atoi(e); if (n > 0 && n <= c->sm_count) gemm_ctas = n; }
@@ -837,8 +859,57 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         for (int i = 1; i <= 8; ++i) fprintf(stderr, " %lld", hh[i] ? hh[i] - hh[0] : -1);
         fprintf(stderr, "  (u | downdate+tt | p,q | deflate | gram+eig | w | P dots | R stream)\n");
     };
+    CvBuf spanbuf(c);
+    const int span_max = 600;
+    int span_n = 0;
+    std::vector<char> span_kind;
+    if (getenv("PLSB_CV_TIMELINE")) {
+        PLSB_TRY(spanbuf.alloc((size_t)2 * span_max * sizeof(unsigned long long)));
+        std::vector<unsigned long long> init((size_t)2 * span_max);
+        for (int i = 0; i < span_max; ++i) { init[2 * i] = ~0ull; init[2 * i + 1] = 0ull; }
+        PLSB_CUDA(cudaMemcpyAsync(spanbuf.p, init.data(), init.size() * sizeof(unsigned long long), cudaMemcpyHostToDevice, c->stream));
+        PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    }
+    auto next_span = [&](char kind) -> unsigned long long * {
+        if (!spanbuf.p || span_n >= span_max) return nullptr;
+        span_kind.push_back(kind);
+        return (unsigned long long *)spanbuf.p + 2 * (span_n++);
+    };
+    auto dump_timeline = [&]() {
+        if (!spanbuf.p || span_n == 0) return;
+        std::vector<unsigned long long> hh((size_t)2 * span_n);
+        cudaStreamSynchronize(c->stream);
+        if (cudaMemcpy(hh.data(), spanbuf.p, hh.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+        const unsigned long long t0 = hh[0];
+        fprintf(stderr, "[plsb] cv timeline (us since the first launch's first CTA): kind start end\n");
+        for (int i = 0; i < span_n; ++i)
+            fprintf(stderr, "[plsb]   %c %10.1f %10.1f\n", span_kind[i], (double)(hh[2 * i] - t0) / 1e3, (double)(hh[2 * i + 1] - t0) / 1e3);
+    };
+    CvBuf ctabuf(c);
+    int cta_a = -1, cta_traced = 0, cta_nf = 0, cta_which = 1;     // which launch with that component: 0 = lane 0's, 1 = lane 1's, ...
+    if (const char *we = getenv("PLSB_CV_CTA_TRACE_WHICH")) cta_which = atoi(we);
+    if (const char *te = getenv("PLSB_CV_CTA_TRACE")) {
+        cta_a = atoi(te);
+        PLSB_TRY(ctabuf.alloc((size_t)3 * 8192 * sizeof(long long)));
+        PLSB_CUDA(cudaMemsetAsync(ctabuf.p, 0, (size_t)3 * 8192 * sizeof(long long), c->stream));
+    }
+    auto dump_cta_trace = [&]() {
+        if (!ctabuf.p || cta_nf == 0) return;
+        std::vector<long long> hh((size_t)3 * cta_nf);
+        cudaStreamSynchronize(c->stream);
+        if (cudaMemcpy(hh.data(), ctabuf.p, hh.size() * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+        const char *path = getenv("PLSB_CV_CTA_TRACE_FILE");
+        FILE *fp = fopen(path ? path : "cta_trace.csv", "w");
+        if (!fp) return;
+        fprintf(fp, "cta,smid,start_ns,end_ns\n");
+        for (int i = 0; i < cta_nf; ++i) fprintf(fp, "%d,%lld,%lld,%lld\n", i, hh[3 * i], hh[3 * i + 1], hh[3 * i + 2]);
+        fclose(fp);
+    };
     auto launch_fold = [&](cudaStream_t st, int a, int nf) -> int {
         v.trace = (a == trace_a && a >= 0 && traced++ == 1) ? (long long *)tracebuf.p : nullptr;   // the second wave's launch
+        v.cta_trace = nullptr;
+        v.span = (a >= 0 && fused) ? next_span('F') : nullptr;
+        if (a == cta_a && a >= 0 && cta_traced++ == cta_which && nf <= 8192) { v.cta_trace = (long long *)ctabuf.p; cta_nf = nf; }
         if (a >= 0 && fused) {
             fused_kern<<<nf, CV_FNT, fsm, st>>>(v);
         } else if (M > PLSB_MAX_M) {
@@ -869,7 +940,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
                 PLSB_TRY(launch_fold(c->stream, a, nf));
             }
         }
-        { dump_trace(); return finish(); }
+        { dump_trace(); dump_cta_trace(); dump_timeline(); return finish(); }
     }
 
     // ---- two lanes ----------------------------------------------------------------------------------------------
@@ -927,7 +998,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
                     PLSB_CUDA(cudaStreamWaitEvent(sx.g, L.evF, 0));            // r_a of this lane is ready
                     {
                         ProfScope ps(c, PLSB_PROF_CV_GEMM, sx.g);
-                        PLSB_TRY(launch_cv_gemm(c, sx.g, Gt.d(), L.Rt.d(), K, ldk, nfl[l], L.Gr.d(), gemm_stages, gemm_ctas));
+                        PLSB_TRY(launch_cv_gemm(c, sx.g, Gt.d(), L.Rt.d(), K, ldk, nfl[l], L.Gr.d(), gemm_stages, gemm_ctas, next_span('G')));
                     }
                     PLSB_CUDA(cudaEventRecord(L.evG, sx.g));
                     PLSB_CUDA(cudaStreamWaitEvent(sx.f, L.evG, 0));
@@ -945,7 +1016,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     PLSB_CUDA(cudaEventRecord(sx.e1, sx.f));
     PLSB_CUDA(cudaStreamWaitEvent(c->stream, sx.e0, 0));
     PLSB_CUDA(cudaStreamWaitEvent(c->stream, sx.e1, 0));
-    { dump_trace(); return finish(); }
+    { dump_trace(); dump_cta_trace(); dump_timeline(); return finish(); }
 }
 
 extern "C" int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,

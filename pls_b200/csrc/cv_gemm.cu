@@ -48,6 +48,7 @@ struct CvGemmArgs {
     const double *Gt, *Rt;
     double *Gr;            // [fold][ldk]
     int K, ldk, nf, nkt, nmt, nnt;
+    unsigned long long *span;   // dev tool (PLSB_CV_TIMELINE): earliest CTA start / latest CTA end of this launch, or null
 };
 
 __device__ __forceinline__ void cg_dmma(double &c0, double &c1, double a, double b) {
@@ -63,6 +64,11 @@ __global__ void __maxnreg__(168) cv_gemm_kernel(const CvGemmArgs g) {
     uint64_t *full = reinterpret_cast<uint64_t *>(smem + (size_t)CG_STAGES * CG_STAGE);
     int *left = reinterpret_cast<int *>(full + CG_STAGES);      // consumer warps that have not yet left the stage
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (g.span && tid == 0) {
+        unsigned long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        atomicMin(g.span, t_);
+    }
     const int nitems = g.nmt * g.nnt;
     const int mine = blockIdx.x < nitems ? (nitems - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
     const int total = mine * g.nkt;                              // k-tiles this CTA consumes
@@ -135,6 +141,11 @@ __global__ void __maxnreg__(168) cv_gemm_kernel(const CvGemmArgs g) {
                 if (n + 1 < g.nf) g.Gr[(int64_t)(n + 1) * g.ldk + m] = acc[i][j][1];
             }
     }
+    if (g.span && tid == 0) {
+        unsigned long long t_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_));
+        atomicMax(g.span + 1, t_);
+    }
 }
 
 int launch_cv_gemm_tile_g(plsb_ctx *c, cudaStream_t st, const double *G, int64_t ldg, int64_t K, double *Gt) {
@@ -146,14 +157,20 @@ int launch_cv_gemm_tile_g(plsb_ctx *c, cudaStream_t st, const double *G, int64_t
 }
 
 int launch_cv_gemm(plsb_ctx *c, cudaStream_t st, const double *Gt, const double *Rt, int64_t K, int64_t ldk, int nf, double *Gr,
-                   int stages, int max_ctas) {
+                   int stages, int max_ctas, unsigned long long *span) {
     CvGemmArgs g{};
     g.Gt = Gt; g.Rt = Rt; g.Gr = Gr; g.K = (int)K; g.ldk = (int)ldk; g.nf = nf;
+    g.span = span;
     g.nkt = (int)ceil_div(K, CG_BK); g.nmt = (int)ceil_div(K, CG_BM); g.nnt = (int)ceil_div(nf, CG_BN);
     const int ns = stages == 2 ? 2 : 3;
     const size_t smem = (size_t)ns * CG_STAGE + ns * sizeof(uint64_t) + ns * sizeof(int) + 16;
     auto kern = ns == 2 ? cv_gemm_kernel<2> : cv_gemm_kernel<3>;
     PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // An SM runs with one shared-memory carve-out at a time and keeps it while anything is resident.  The 2-stage kernel
+    // (141 KB) would be given the 164 KB carve-out, and a fold CTA of the other lane (69 KB) could then not join it on an
+    // SM it reached first — seen in the launch timeline (PLSB_CV_TIMELINE) as fold launches that only started once the
+    // product's CTAs were leaving.  Ask for the maximum, like the fold kernels do.
+    PLSB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
     const int nitems = g.nmt * g.nnt;
     int grid = nitems < c->sm_count ? nitems : c->sm_count;
     if (max_ctas > 0 && grid > max_ctas) grid = max_ctas;     // SMs left entirely to the other lane's fold kernel (cv.cu)

@@ -194,7 +194,7 @@ size_t cv_gemm_gt_doubles(int64_t K);
 size_t cv_gemm_rt_doubles(int64_t K, int64_t F);
 int launch_cv_gemm_tile_g(plsb_ctx *c, cudaStream_t st, const double *G, int64_t ldg, int64_t K, double *Gt);
 int launch_cv_gemm(plsb_ctx *c, cudaStream_t st, const double *Gt, const double *Rt, int64_t K, int64_t ldk, int nf, double *Gr,
-                   int stages, int max_ctas);
+                   int stages, int max_ctas, unsigned long long *span = nullptr);
 
 // ---- synthetic data (synth.cu) ----------------------------------------------------------------
 int launch_synth(plsb_ctx *c, uint64_t seed, int64_t row0, int64_t N, int64_t K, int64_t M, int64_t L,
