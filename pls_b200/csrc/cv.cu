@@ -833,9 +833,10 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     }
     {   // the TMA-fed ring for the orthogonalisation stream
         const char *re = getenv("PLSB_CV_RING");
-        int ns = kpt8 ? 3 : 4;                        // PLSB_CV_RING = 0 (plain loads) or the number of 16 KB slots
-                                                      // (K <= 2048: a slot is a whole row; 3 slots let four CTAs share an SM)
-        if (re) { ns = atoi(re); if (ns == 1) ns = kpt8 ? 3 : 4; if (ns > CR_NSLOT_MAX) ns = CR_NSLOT_MAX; if (ns < 0) ns = 0; }
+        int ns = 3;                                   // PLSB_CV_RING = 0 (plain loads) or the number of 16 KB slots;
+                                                      // three: 53 KB per CTA, so that FOUR 64-register CTAs share a free SM
+                                                      // (slot model, DESIGN 3.6: 6.0 -> 5.8 ms per wave-component at C5)
+        if (re) { ns = atoi(re); if (ns == 1) ns = 3; if (ns > CR_NSLOT_MAX) ns = CR_NSLOT_MAX; if (ns < 0) ns = 0; }
         v.ring = fused ? ns : 0;
         if (v.ring) {
             const int fsm_max = (int)cr_smem(CR_NSLOT_MAX);

@@ -11,9 +11,22 @@
 #include <cstdint>
 #include <numeric>
 #include <random>
+#include <thread>
 #include <vector>
 
 #include "../../include/plsb.h"
+
+// fn(m) for every response m; on a few threads when the block is large (each response's sums and ranks are computed by
+// one thread in the reference's order, so results do not depend on the thread count)
+template <typename Fn>
+static void over_responses(int64_t M, int64_t work_per_response, Fn fn) {
+    const int64_t nthr = work_per_response >= (1 << 18) ? std::min<int64_t>(M, std::max(1u, std::thread::hardware_concurrency())) : 1;
+    if (nthr <= 1) { for (int64_t m = 0; m < M; ++m) fn(m); return; }
+    std::vector<std::thread> th;
+    for (int64_t t = 0; t < nthr; ++t)
+        th.emplace_back([=] { for (int64_t m = t; m < M; m += nthr) fn(m); });
+    for (auto &x : th) x.join();
+}
 
 extern "C" {
 
@@ -53,13 +66,14 @@ double plsb_wilcoxon(const double *e1, const double *e2, int64_t n) {
 int plsb_validation(const double *E, int64_t M, int64_t rows, int64_t A, int out_type, double *out) {
     // out: M x A column-major; out_type 0 = RESS, 1 = MSE (pls.cpp:235-261)
     if (!E || !out || M < 0 || rows < 0 || A < 0) return PLSB_ERR_ARG;
-    for (int64_t m = 0; m < M; ++m)
+    over_responses(M, rows * A, [=](int64_t m) {
         for (int64_t c = 0; c < A; ++c) {
             const double *e = E + ((size_t)m * A + c) * rows;
             double s = 0.0;
             for (int64_t i = 0; i < rows; ++i) s += e[i] * e[i];
             out[c * M + m] = out_type == 0 ? s : s / (double)rows;
         }
+    });
     return PLSB_OK;
 }
 
@@ -67,10 +81,11 @@ int plsb_optimal_num_components(const double *E, int64_t M, int64_t rows, int64_
     if (!E || !out || A < 1) return PLSB_ERR_ARG;
     std::vector<double> press((size_t)(M * A));
     plsb_validation(E, M, rows, A, 0, press.data());
-    for (int64_t m = 0; m < M; ++m) {
+    const double *pr = press.data();
+    over_responses(M, rows * A, [=](int64_t m) {
         int64_t ref = 0;  // first minimum, like Eigen's minCoeff
         for (int64_t c = 1; c < A; ++c)
-            if (press[(size_t)(c * M + m)] < press[(size_t)(ref * M + m)]) ref = c;
+            if (pr[(size_t)(c * M + m)] < pr[(size_t)(ref * M + m)]) ref = c;
         int64_t pick = ref;
         const double *e_ref = E + ((size_t)m * A + ref) * rows;
         for (int64_t alt = 0; alt < ref; ++alt) {
@@ -78,7 +93,7 @@ int plsb_optimal_num_components(const double *E, int64_t M, int64_t rows, int64_
             if (plsb_wilcoxon(e_ref, e_alt, rows) > alpha) { pick = alt; break; }
         }
         out[m] = pick + 1;
-    }
+    });
     return PLSB_OK;
 }
 

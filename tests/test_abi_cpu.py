@@ -48,6 +48,18 @@ def test_host_stats_match_reference_goldens():
     assert relerr(_capi.validation(g["lso"], 1), g["lso_mse"]) <= RTOL
 
 
+def test_summaries_of_a_large_block_are_threaded_and_unchanged():
+    """validation / optimal_num_components split a large residual block over host threads by response; every response is
+    still summed and ranked by one thread in the reference's order: the oracle's single-threaded answers, bit for bit."""
+    from oracle import port
+    rng = np.random.default_rng(11)
+    M, rows, A = 5, 40000, 9                     # rows * A >= 2^18: the threaded path
+    E = rng.standard_normal((M, rows, A)) * (1.0 + 0.3 * rng.standard_normal((M, 1, A)) ** 2)
+    assert np.array_equal(_capi.validation(E, 0), port.validation(E, 0))
+    assert np.array_equal(_capi.validation(E, 1), port.validation(E, 1))
+    assert np.array_equal(_capi.optimal_num_components(E), port.optimal_num_components(E))
+
+
 @pytest.mark.parametrize("name,N,trials", [("c1_toy", 10, 100), ("c2_nir_octane", 60, 600), ("c3_nir_pls2", 60, 1000)])
 def test_lso_folds_match_reference(name, N, trials):
     g = load_golden(name)
