@@ -388,7 +388,7 @@ static int env_int(const char *name, int dflt) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// Wide matrices (K > 4096): a row tile no longer fits the shared-memory ring, so the component pass falls back
+// Very wide matrices (K > 8192): a row no longer fits the shared-memory ring three times, so the component pass falls back
 // to two plain streaming kernels — t = X r, then [g | tt] = [X't | t't] — and X'Y to the second one with Y's
 // columns in the role of t.  Two reads of X per component (what the reference does, pls.cpp:419-421); every
 // element is still read with coalesced 128-bit loads and summed without atomics.
@@ -573,6 +573,10 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
         if (rbsel == 4) return run_fused<512, 512, 8, 4>(c, ds, r, out, t_out, across_ranks);
         return run_fused<512, 512, 8, 2>(c, ds, r, out, t_out, across_ranks);
     }
+    // 4096 < K <= 8192: one 64 KB row per tile, 16 columns per thread (x, the accumulators and r: 48 doubles = 96 of the
+    // 128 registers a 512-thread CTA may use), three rows in flight per SM — still ONE read of X per component.  The
+    // two-kernel fallback below (two reads) ran these shapes at 0.46 of this bound.  PLSB_PASS_WIDE_V1=1: A/B.
+    if (ldk <= 8192 && !getenv("PLSB_PASS_WIDE_V1")) return run_fused<512, 512, 16, 1>(c, ds, r, out, t_out, across_ranks);
     return run_wide_fused(c, ds, r, out, t_out, across_ranks);
 }
 
