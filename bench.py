@@ -478,6 +478,7 @@ def run_ours(args):
         e2e = {"value": 1.0 / e2e_s, "unit": "fits/s", "h2d_bytes_per_step": int(8 * rows * (K + M)),
                "d2h_bytes_per_step": int(8 * (3 * K * A + M * A + rows * A)), "ms_per_step": e2e_s * 1e3,
                "steps": args.e2e_steps, "what": "plsb_dataset_create(pinned host X,Y) + plsb_fit + W,P,R,Q,T to host",
+               "h2d_GBps_rank0": 8.0 * rows * (K + M) / (up_ms / max(args.e2e_steps, 1) * 1e-3) / 1e9 if up_ms > 0 else None,
                "device_ms_rank0": {"upload_incl_xtx_xty_under_the_transfer": up_ms / max(args.e2e_steps, 1),
                                    "fit_after_upload": fit_ms / max(nf, 1), "of_which_scores_T": sc_ms / max(nf, 1)},
                "path": ("X'X and X'Y accumulated on the tensor cores while the rows cross PCIe; components from the "

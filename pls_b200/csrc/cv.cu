@@ -765,18 +765,30 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
     int gemm_ctas = c->sm_count;
     if (lanes == 2) {
         if (const char *e = getenv("PLSB_CVG_CTAS")) { const int n = atoi(e); if (n > 0 && n <= c->sm_count) gemm_ctas = n; }
-        // equal waves, an even number of them: the count whose product items (row tiles x 128-fold column tiles) fill
-        // whole rounds of gemm_ctas CTAs best
-        const int64_t nmt = ceil_div(K, 128), nw0 = 2 * ceil_div(nfolds_local, 2 * F);
-        int64_t best_nw = nw0, best_cost = -1;
+        // Wave size: the one whose product items (row tiles x 128-fold column tiles) fill whole rounds of gemm_ctas CTAs
+        // best over the call — equal waves (an even number of them), or whole-tile waves with a ragged last one.  Ties:
+        // an even wave count (both lanes busy to the end), then fewer waves.
+        const int64_t nmt = ceil_div(K, 128), Fcap = F;
+        auto rounds = [&](int64_t folds) { return folds > 0 ? ceil_div(nmt * ceil_div(folds, 128), (int64_t)gemm_ctas) : (int64_t)0; };
+        int64_t best_F = 0, best_cost = -1, best_waves = 0;
+        auto consider = [&](int64_t Fc) {
+            if (Fc < 1 || Fc > Fcap) return;
+            const int64_t nfull = nfolds_local / Fc, rem = nfolds_local % Fc, waves = nfull + (rem > 0 ? 1 : 0);
+            if (waves < 2) return;
+            const int64_t cost = nfull * rounds(Fc) + rounds(rem);
+            const bool better = best_cost < 0 || cost < best_cost ||
+                                (cost == best_cost && ((waves % 2 == 0) > (best_waves % 2 == 0) ||
+                                                       ((waves % 2 == 0) == (best_waves % 2 == 0) && waves < best_waves)));
+            if (better) { best_cost = cost; best_F = Fc; best_waves = waves; }
+        };
+        const int64_t nw0 = 2 * ceil_div(nfolds_local, 2 * Fcap);
         for (int64_t nw = nw0; nw <= (4 * nw0 > nw0 + 12 ? 4 * nw0 : nw0 + 12); nw += 2) {
-            const int64_t Fw = ceil_div(nfolds_local, nw), nnt = ceil_div(Fw, 128);
-            const int64_t cost = nw * ceil_div(nmt * nnt, gemm_ctas);
-            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_nw = nw; }
+            const int64_t Fw = ceil_div(nfolds_local, nw);
+            consider(Fw);
             if (Fw <= 256) break;
         }
-        const int64_t Fe = ceil_div(nfolds_local, best_nw);
-        if (Fe < F) F = Fe;
+        for (int64_t Fc = 256; Fc <= Fcap; Fc += 128) consider(Fc);
+        if (best_F > 0) F = best_F;
     }
     if (F > nfolds_local) F = nfolds_local;
 

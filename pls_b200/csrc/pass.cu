@@ -428,7 +428,22 @@ __global__ void __launch_bounds__(256) wide_xtv_kernel(const double *__restrict_
         double a0[NV], a1[NV];
 #pragma unroll
         for (int v = 0; v < NV; ++v) { a0[v] = 0.0; a1[v] = 0.0; }
-        for (int64_t i = r0; i < r1; ++i) {
+        int64_t i = r0;
+        for (; i + 4 <= r1; i += 4) {      // four rows in flight per thread; the sums stay in ascending row order
+            double2 x[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) x[u] = *reinterpret_cast<const double2 *>(X + (i + u) * ldk + c0);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+#pragma unroll
+                for (int v = 0; v < NV; ++v) {
+                    const double y = v < nv ? V[(i + u) * ldv + v0 + v] : 0.0;
+                    a0[v] = fma(x[u].x, y, a0[v]);
+                    a1[v] = fma(x[u].y, y, a1[v]);
+                }
+            }
+        }
+        for (; i < r1; ++i) {
             const double2 x = *reinterpret_cast<const double2 *>(X + i * ldk + c0);
 #pragma unroll
             for (int v = 0; v < NV; ++v) {
@@ -566,6 +581,7 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
         // faster, at 8 GB and 16 GB the one-CTA shape is 3-7 % faster — hence the size threshold.)
         const bool big = ds->N * ldk >= 3 * ((int64_t)1 << 28) && !getenv("PLSB_PASS_CTAS_PER_SM");
         if (rbsel == 2) return run_fused<256, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
+        if (rbsel == 44) return run_fused<512, 512, 4, 4>(c, ds, r, out, t_out, across_ranks);   // A/B: one row group, 4 columns per thread
         if (rbsel == 12 || (rbsel == 0 && big)) return run_fused<512, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
         return run_fused<256, 256, 8, 4>(c, ds, r, out, t_out, across_ranks);
     }
