@@ -36,6 +36,7 @@ struct CvArgs {
     double *Rt;                // two-lane engine: the next r also goes here, in the tiled layout of cv_gemm.cu (or null)
     int nkt;
     double *wide;              // M > 32: per-fold scratch of wide_scratch_doubles(M) doubles (step_wide.cuh), else null
+    int wide_jac_smem;         // M > 32: the Jacobi work area is the kernel's dynamic shared memory
     int prefetch;              // fused kernel: run its HBM streams ahead into L2 with bulk prefetches
     int ring;                  // fused kernel: P_f / R_f rows arrive through a TMA-fed shared-memory ring (dynamic smem)
     long long *trace;          // dev tool (PLSB_CV_TRACE=<component>): globaltimer ns at the fused kernel's phase boundaries
@@ -117,7 +118,11 @@ __global__ void __launch_bounds__(CV_NT) cv_fold_kernel(const CvArgs v) {
     }
     const int an = v.a + 1;
     if (an >= v.A) return;
-    if constexpr (WIDE) next_weights_wide<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, wide, sh);
+    if constexpr (WIDE) {
+        extern __shared__ __align__(16) double cvw_dyn[];
+        next_weights_wide<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, wide, sh,
+                                 v.wide_jac_smem ? cvw_dyn : nullptr);
+    }
     else next_weights<CV_NT>(K, ldk, M, an, Sf, Pf, Rf, v.w + (size_t)f * ldk, Rf + (size_t)an * ldk, sh);
     if (v.Rt) {   // (every thread re-reads the elements it wrote itself: same k -> thread mapping as next_weights)
         const double *rn = Rf + (size_t)an * ldk;
@@ -856,6 +861,13 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         }
     }
     const size_t fsm = v.ring ? cr_smem(v.ring) : 0;
+    size_t wide_jsm = 0;
+    if (M > PLSB_MAX_M) {
+        wide_jsm = wide_jacobi_smem_doubles((int)M) * sizeof(double);
+        if (wide_jsm + 4096 > c->smem_optin) wide_jsm = 0;
+        if (wide_jsm) PLSB_CUDA(cudaFuncSetAttribute(cv_fold_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wide_jsm));
+    }
+    v.wide_jac_smem = wide_jsm ? 1 : 0;
     CvBuf tracebuf(c);
     int trace_a = -1, traced = 0;
     if (const char *te = getenv("PLSB_CV_TRACE")) {
@@ -926,7 +938,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
         if (a >= 0 && fused) {
             fused_kern<<<nf, CV_FNT, fsm, st>>>(v);
         } else if (M > PLSB_MAX_M) {
-            cv_fold_kernel<true><<<nf, CV_NT, 0, st>>>(v);
+            cv_fold_kernel<true><<<nf, CV_NT, wide_jsm, st>>>(v);
         } else {
             cv_fold_kernel<false><<<nf, CV_NT, 0, st>>>(v);
         }

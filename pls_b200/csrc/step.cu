@@ -27,15 +27,17 @@ __global__ void __launch_bounds__(STEP_NT) step_kernel(const StepArgs s) {
 }
 
 // Wide response blocks (M > 32): the general path of step_wide.cuh, one CTA, M-sized objects in global scratch.
-__global__ void __launch_bounds__(STEP_NT) step_wide_kernel(const StepArgs s) {
+__global__ void __launch_bounds__(STEP_NT) step_wide_kernel(const StepArgs s, const int jac_in_smem) {
     __shared__ WideSmem<STEP_NT> sh;
+    extern __shared__ __align__(16) double wide_dyn[];
     const int ldk = s.ldk;
     if (s.a >= 0)
         finish_component_wide<STEP_NT>(s.K, ldk, s.M, s.S, s.g, s.g[ldk], s.R + (size_t)s.a * ldk, s.P + (size_t)s.a * ldk,
                                        s.Q + (size_t)s.a * s.M, s.wide);
     const int an = s.a + 1;
     if (an >= s.A) return;
-    next_weights_wide<STEP_NT>(s.K, ldk, s.M, an, s.S, s.P, s.R, s.W + (size_t)an * ldk, s.R + (size_t)an * ldk, s.wide, sh);
+    next_weights_wide<STEP_NT>(s.K, ldk, s.M, an, s.S, s.P, s.R, s.W + (size_t)an * ldk, s.R + (size_t)an * ldk, s.wide, sh,
+                               jac_in_smem ? wide_dyn : nullptr);
 }
 size_t step_wide_scratch_bytes(int M) { return M > PLSB_MAX_M ? wide_scratch_doubles(M) * sizeof(double) : 0; }
 
@@ -393,9 +395,12 @@ static int launch_step_cluster(plsb_ctx *c, const StepArgs &s) {
 int launch_step(plsb_ctx *c, const StepArgs &s) {
     if (s.M > PLSB_MAX_M) {   // wide response block: the general one-CTA path
         PLSB_ARG(s.wide, "internal: no scratch for the wide-response step");
+        size_t jsm = wide_jacobi_smem_doubles(s.M) * sizeof(double);
+        if (jsm + 4096 > c->smem_optin) jsm = 0;                 // too wide for one SM: iterate in the global scratch
+        if (jsm) PLSB_CUDA(cudaFuncSetAttribute(step_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)jsm));
         {
             ProfScope ps(c, PLSB_PROF_STEP);
-            step_wide_kernel<<<1, STEP_NT, 0, c->stream>>>(s);
+            step_wide_kernel<<<1, STEP_NT, jsm, c->stream>>>(s, jsm ? 1 : 0);
         }
         c->launches++;
         PLSB_CUDA(cudaGetLastError());

@@ -129,6 +129,98 @@ __device__ void jacobi_dominant_cta(double *A, double *V, int m, double *q, doub
     __syncthreads();
 }
 
+// 2^(-ilogb(x)) for a positive normal double (the same exact power-of-two scaling as step_cluster.cuh's solver)
+__device__ __forceinline__ double wide_pow2_scale(double x) {
+    const long long e = (__double_as_longlong(x) >> 52) & 0x7ff;
+    return __longlong_as_double((2046LL - e) << 52);
+}
+
+// Dominant unit eigenvector of the symmetric PSD m x m matrix G by REPEATED SQUARING, run by the whole CTA — the
+// algorithm of step_cluster.cuh's warp solver (B <- B^2 with lazy exact power-of-two scaling until trace(B^2)/trace(B)^2
+// is within 1e-9 of 1, three more squarings, then two power steps with G itself to remove the rounding the squarings
+// left) for matrices too wide for one warp.  work: SHARED memory, wide_squaring_smem_doubles(m) doubles (a copy of G and
+// two iterates at an odd row stride: conflict-free).  A squaring is m^3 FMAs over NT threads: ~2 us at m = 64, where a
+// Jacobi sweep costs 63 rounds of three CTA barriers each and ten to sixty sweeps are needed.  Returns false when 48
+// squarings were not enough (near-degenerate spectrum) or the matrix is zero: the caller falls back to Jacobi.
+__host__ __device__ inline size_t wide_squaring_smem_doubles(int m) { return 3 * (size_t)m * (size_t)(m | 1); }
+
+template <int NT>
+__device__ bool dominant_eigvec_cta(const double *G, double *work, int m, double *q, WideSmem<NT> &sh) {
+    const int tid = threadIdx.x;
+    const int ld = m | 1;
+    double *Gs = work, *buf[2] = {work + (size_t)m * ld, work + 2 * (size_t)m * ld};
+    for (int e = tid; e < m * m; e += NT) {
+        const double v = G[e];
+        Gs[(e / m) * ld + e % m] = v;
+        buf[0][(e / m) * ld + e % m] = v;
+    }
+    __syncthreads();
+    double tr = 0.0;
+    for (int i = 0; i < m; ++i) tr += Gs[i * ld + i];
+    if (!(tr > 0.0) || !(tr < 1e300)) return false;
+    int cur = 0, extra = 0, res = -1;
+    double sc = wide_pow2_scale(tr), trB = sc * tr;
+    for (int it = 0; it < 48; ++it) {
+        const double *B = buf[cur];
+        double *C = buf[cur ^ 1];
+        const double sc2 = sc * sc;
+        for (int e = tid; e < m * m; e += NT) {
+            const int i = e / m, j = e % m;               // (B^2)_ij = row_i . row_j by symmetry
+            const double *bi = B + (size_t)i * ld, *bj = B + (size_t)j * ld;
+            double a0 = 0.0, a1 = 0.0;
+            int k = 0;
+            for (; k + 1 < m; k += 2) {
+                a0 = fma(bi[k], bj[k], a0);
+                a1 = fma(bi[k + 1], bj[k + 1], a1);
+            }
+            if (k < m) a0 = fma(bi[k], bj[k], a0);
+            C[(size_t)i * ld + j] = (a0 + a1) * sc2;
+        }
+        __syncthreads();
+        double trC = 0.0;
+        for (int k = 0; k < m; ++k) trC += C[(size_t)k * ld + k];     // every thread: the same sum in the same order
+        const double t2 = trB * trB;
+        cur ^= 1;
+        if (!(trC > 0.0)) break;
+        if (t2 - trC <= 1e-9 * t2 && ++extra > 2) { res = cur; break; }
+        sc = wide_pow2_scale(trC);
+        trB = sc * trC;
+        __syncthreads();       // the buffer read in this iteration is overwritten in the next one
+    }
+    __syncthreads();
+    if (res < 0) return false;
+    const double *B = buf[res];
+    int col = 0;
+    double best = -1.0;
+    for (int i = 0; i < m; ++i) {
+        const double d = B[(size_t)i * ld + i];
+        if (d > best) { best = d; col = i; }
+    }
+    double *x = buf[res ^ 1];          // free now: x at [0, m), G x at [m, 2m)
+    for (int k = tid; k < m; k += NT) x[k] = B[(size_t)k * ld + col];
+    __syncthreads();
+    for (int rep = 0; rep < 3; ++rep) {  // normalise, then v <- G v (twice)
+        double n2 = 0.0;
+        for (int k = 0; k < m; ++k) n2 = fma(x[k], x[k], n2);
+        const double nrm = sqrt(n2);
+        __syncthreads();
+        for (int k = tid; k < m; k += NT) x[k] = x[k] / nrm;
+        __syncthreads();
+        if (rep == 2) break;
+        for (int i = tid; i < m; i += NT) {
+            double acc = 0.0;
+            for (int k = 0; k < m; ++k) acc = fma(Gs[(size_t)i * ld + k], x[k], acc);
+            x[m + i] = acc;
+        }
+        __syncthreads();
+        for (int k = tid; k < m; k += NT) x[k] = x[m + k];
+        __syncthreads();
+    }
+    for (int k = tid; k < m; k += NT) q[k] = x[k];
+    __syncthreads();
+    return true;
+}
+
 // one warp per dot product (the same order of operations as step_core.cuh's warp_dots)
 template <int NT, typename FA, typename FB>
 __device__ __forceinline__ void wide_warp_dots(int ndots, int K, FA a_of, FB b_of, double *out) {
@@ -172,12 +264,22 @@ __device__ void finish_component_wide(int K, int ldk, int M, double *S, const do
 }
 
 // Weight and rotation vectors of component `an` (M > 1 assumed: wide).
+// jac: optional SHARED-memory work area of wide_jacobi_smem_doubles(M) doubles (the kernel's dynamic shared memory) for
+// the Jacobi iteration — every tournament round is a few dependent loads and stores per thread, and out of global
+// memory a round costs ~4 us of L2 round trips (measured: 2.0 ms per component at M = 40, 8.2 ms at M = 64); null:
+// the global scratch is used (M too wide for one SM's shared memory).
+__host__ __device__ inline size_t wide_jacobi_smem_doubles(int M) {
+    const size_t jac = 2 * (size_t)M * M + 4 * (size_t)((M + 1) / 2), sq = wide_squaring_smem_doubles(M);
+    return jac > sq ? jac : sq;
+}
+
 template <int NT>
 __device__ void next_weights_wide(int K, int ldk, int M, int an, const double *S, const double *P, const double *R,
-                                  double *w, double *rn, double *wide, WideSmem<NT> &sh) {
+                                  double *w, double *rn, double *wide, WideSmem<NT> &sh, double *jac = nullptr) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     double *gram = wide, *V = wide + (size_t)M * M, *q = V + (size_t)M * M, *rot = q + M;
     double *pairs = rot + 2 * ((M + 1) / 2);
+    if (jac) { gram = jac; V = jac + (size_t)M * M; rot = V + (size_t)M * M; pairs = rot + 2 * ((M + 1) / 2); }
     const int npairs = M * (M + 1) / 2;
     for (int d = warp; d < npairs; d += NT / 32) {   // Gram = S'S, upper triangle, one warp per entry
         int u = 0, rem = d;
@@ -192,13 +294,23 @@ __device__ void next_weights_wide(int K, int ldk, int M, int an, const double *S
         }
         for (; k < K; k += 32) s0 = fma(pa[k], pb[k], s0);
         const double sum = warp_sum(s0 + s1);
-        if (lane == 0) {
-            gram[u * M + v] = sum;
-            gram[v * M + u] = sum;
+        if (lane == 0) {              // the Gram matrix itself always goes to the global scratch (wide[0 .. M*M))
+            wide[u * M + v] = sum;
+            wide[v * M + u] = sum;
         }
     }
     __syncthreads();
-    jacobi_dominant_cta<NT>(gram, V, M, q, rot, pairs, sh);
+    // shared-memory work area: repeated squaring first (the Gram matrix still sits in the global scratch), Jacobi as
+    // the fallback for near-degenerate spectra — and the only solver when M is too wide for one SM's shared memory
+    bool solved = false;
+    if (jac) solved = dominant_eigvec_cta<NT>(wide, jac, M, q, sh);
+    if (!solved) {
+        if (jac) {
+            for (int e = tid; e < M * M; e += NT) gram[e] = wide[e];
+            __syncthreads();
+        }
+        jacobi_dominant_cta<NT>(gram, V, M, q, rot, pairs, sh);
+    }
     for (int k = tid; k < ldk; k += NT) {
         double acc = 0.0;
         if (k < K)
