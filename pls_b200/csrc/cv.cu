@@ -39,6 +39,7 @@ struct CvArgs {
     int wide_jac_smem;         // M > 32: the Jacobi work area is the kernel's dynamic shared memory
     int prefetch;              // fused kernel: run its HBM streams ahead into L2 with bulk prefetches
     int ring;                  // fused kernel: P_f / R_f rows arrive through a TMA-fed shared-memory ring (dynamic smem)
+    int ring_pf;               // ... and the item this many places ahead of each issued one is prefetched into L2
     long long *trace;          // dev tool (PLSB_CV_TRACE=<component>): globaltimer ns at the fused kernel's phase boundaries
     long long *cta_trace;      // dev tool (PLSB_CV_CTA_TRACE=<component>): per CTA (smid, start ns, end ns) of one launch
     unsigned long long *span;  // dev tool (PLSB_CV_TIMELINE=1): [2] = earliest CTA start / latest CTA end of THIS launch (ns)
@@ -231,6 +232,15 @@ struct FoldRing {
     char *base; uint64_t *full; int *left;
     const double *Pf, *Rf;
     int a, nch, ldk, nP, nitems, ns; // nP: items of the P part (a rows x nch chunks); then (a + 1) rows of R; ns: slots
+    int pf;                          // > 0: item it + pf is prefetched into L2 when item it is issued (costs no shared memory)
+    __device__ __forceinline__ void prefetch(int it) const {     // one thread
+        if (it >= nitems) return;
+        const bool isR = it >= nP;
+        const int e = isR ? it - nP : it;
+        const int row = e / nch, ch = e % nch;
+        int cols = ldk - ch * CR_CH; cols = cols > CR_CH ? CR_CH : cols;
+        l2_prefetch((isR ? Rf : Pf) + (size_t)row * ldk + (size_t)ch * CR_CH, (uint32_t)cols * 8u);
+    }
     __device__ __forceinline__ void issue(int it) const {        // one thread
         const int slot = it % ns;
         const bool isR = it >= nP;
@@ -240,6 +250,7 @@ struct FoldRing {
         const double *src = (isR ? Rf : Pf) + (size_t)row * ldk + (size_t)ch * CR_CH;
         mbar_arrive_expect_tx(&full[slot], (uint32_t)cols * 8u);
         bulk_g2s(base + (size_t)slot * CR_CH * 8, src, (uint32_t)cols * 8u, &full[slot]);
+        if (pf > 0) prefetch(it + pf);
     }
     __device__ __forceinline__ const double *acquire(int it) const {
         const int slot = it % ns;
@@ -298,7 +309,7 @@ __global__ void __launch_bounds__(CV_FNT, MINB) cv_fold_fused_kernel(const CvArg
     FoldRing ring;
     const bool use_ring = v.ring != 0 && a + 1 < v.A;     // (a CTA that returns before the stream is read must not start it)
     if (use_ring) {
-        ring.ns = v.ring;
+        ring.ns = v.ring; ring.pf = v.ring_pf;
         ring.base = cr_dyn;
         ring.full = reinterpret_cast<uint64_t *>(cr_dyn + (size_t)ring.ns * CR_CH * 8);
         ring.left = reinterpret_cast<int *>(ring.full + ring.ns);
@@ -310,6 +321,7 @@ __global__ void __launch_bounds__(CV_FNT, MINB) cv_fold_fused_kernel(const CvArg
             for (int sl = 0; sl < ring.ns; ++sl) { mbar_init(&ring.full[sl], 1); ring.left[sl] = CV_FNT / 32; }
             mbar_fence_init();
             for (int it = 0; it < ring.ns && it < ring.nitems; ++it) ring.issue(it);   // rows 0.. are final: start now
+            for (int it = ring.ns; ring.pf > 0 && it < ring.ns + ring.pf; ++it) ring.prefetch(it);
         }
         __syncthreads();
     }
@@ -855,6 +867,7 @@ extern "C" int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int
                                                       // (slot model, DESIGN 3.6: 6.0 -> 5.8 ms per wave-component at C5)
         if (re) { ns = atoi(re); if (ns == 1) ns = 3; if (ns > CR_NSLOT_MAX) ns = CR_NSLOT_MAX; if (ns < 0) ns = 0; }
         v.ring = fused ? ns : 0;
+        { const char *pe = getenv("PLSB_CV_RING_PF"); v.ring_pf = pe ? atoi(pe) : 0; }
         if (v.ring) {
             const int fsm_max = (int)cr_smem(CR_NSLOT_MAX);
             PLSB_CUDA(cudaFuncSetAttribute(fused_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, fsm_max));

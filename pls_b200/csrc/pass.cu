@@ -581,7 +581,6 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
         // faster, at 8 GB and 16 GB the one-CTA shape is 3-7 % faster — hence the size threshold.)
         const bool big = ds->N * ldk >= 3 * ((int64_t)1 << 28) && !getenv("PLSB_PASS_CTAS_PER_SM");
         if (rbsel == 2) return run_fused<256, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
-        if (rbsel == 44) return run_fused<512, 512, 4, 4>(c, ds, r, out, t_out, across_ranks);   // A/B: one row group, 4 columns per thread
         if (rbsel == 12 || (rbsel == 0 && big)) return run_fused<512, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
         return run_fused<256, 256, 8, 4>(c, ds, r, out, t_out, across_ranks);
     }

@@ -16,8 +16,7 @@ t0 = time.time()
 ds = _capi.Dataset(ctx, synth=(20260004, 0, N, K, M, 16))
 print(f"synth {N}x{K} in {time.time()-t0:.2f}s", flush=True)
 ctx.profile(True)
-variants = [dict(), dict(PLSB_PASS_RB="44"), dict(), dict(PLSB_PASS_RB="44")] if "--shapes" in sys.argv else \
-    [dict(), dict(PLSB_STEP_V1="1"), dict(PLSB_PASS_RB="4"), dict(PLSB_PASS_STAGES="3")]
+variants = [dict(), dict(PLSB_STEP_V1="1"), dict(PLSB_PASS_RB="4"), dict(PLSB_PASS_STAGES="3")]
 for v in variants:
     for k in ("PLSB_PASS_RB", "PLSB_PASS_STAGES", "PLSB_PASS_CTAS_PER_SM", "PLSB_STEP_V1"):
         os.environ.pop(k, None)
