@@ -82,6 +82,8 @@ def test_c5s_loo(ctx):
                                            # K >= 1024: the fused per-component fold kernel, every M variant
                                            (90, 1100, 3, 5, 1, 40), (60, 2049, 1, 4, 7, 12), (50, 4096, 8, 4, 2, 9),
                                            (70, 1024, 2, 6, 20, 6), (40, 1500, 5, 9, 1, 40),
+                                           # 8 columns per thread (K <= 2048) with every M variant, ragged K
+                                           (64, 1536, 8, 5, 2, 20), (48, 2048, 6, 4, 1, 30), (52, 1026, 4, 7, 5, 11),
                                            # M > 32: per-fold scratch in global memory (step_wide.cuh)
                                            (80, 45, 36, 4, 3, 12), (60, 1100, 34, 3, 1, 10)])
 def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
@@ -149,6 +151,22 @@ def test_two_lane_engine_equals_one_lane_and_the_oracle(ctx, N, K, M, A, monkeyp
     assert relerr(two[:, pick, :], want) <= RTOL
     press = ds.cv_press(A, 0, te)
     assert relerr(press, (two ** 2).sum(axis=1)) <= 1e-13
+    ds.close()
+
+
+def test_two_lane_engine_with_several_held_out_rows(ctx, monkeypatch):
+    """leave-some-out folds (3 held-out rows) through the two-lane engine: the downdate subtracts three rows per fold"""
+    monkeypatch.setenv("PLSB_CV_NO_SMALL", "1")
+    N, K, M, A, ts, nf = 500, 1300, 3, 4, 3, 600
+    X, Y = port.synth(313, N, K, M, L=4)
+    rng = np.random.default_rng(5)
+    te = np.stack([rng.permutation(N)[:ts] for _ in range(nf)]).astype(np.int64)
+    ds = _capi.Dataset(ctx, X, Y)
+    got = ds.cv_folds(A, 0, te)                                   # [M][nf*ts][A]
+    pick = np.array([0, 1, 299, 300, 599])
+    want = port.cv_folds(X, Y, A, 0, te[pick])
+    rows = (pick[:, None] * ts + np.arange(ts)[None, :]).ravel()
+    assert relerr(got[:, rows, :], want) <= RTOL
     ds.close()
 
 
