@@ -6,9 +6,11 @@
 // The reference never re-centres folds (z-scoring happens once, in the CLI), so a fold's cross products
 // are low-rank downdates of the full ones:
 //      S_f = X'Y - X_H' Y_H ,      (X'X)_f r = (X'X) r - X_H' (X_H r)       H = held-out rows of fold f.
-// Per component the whole wave of F folds shares ONE FP64 DMMA GEMM  (X'X) [r_1 .. r_F]  (gemm.cu), and a
-// one-CTA-per-fold kernel does the K-sized algebra (downdate, tt, p, q, deflation of S_f, next w and r —
-// the same code as the single-fit step, step_core.cuh).  The scores of the held-out rows, u = X_H r_a,
+// Per component the whole wave of F folds shares ONE FP64 DMMA product  (X'X) [r_1 .. r_F]  (cv_gemm.cu; gemm.cu for
+// the one-lane path), and a one-CTA-per-fold kernel does the K-sized algebra (downdate, tt, p, q, deflation of S_f,
+// next w and r): the fused kernel below for 1024 <= K <= 4096, M <= 8, else the phase-by-phase code of the single-fit
+// step (step_core.cuh; step_wide.cuh for M > 32).  Two waves are kept in flight so that the tensor-bound product of
+// one runs under the HBM-bound fold kernel of the other.  Small data sets take cv_small.cu instead.  The scores of the held-out rows, u = X_H r_a,
 // fall out of the downdate, so the residuals for every prefix 1..A are a running update
 // e_a = e_{a-1} - u q_a' : no separate prediction pass.
 // Components are extracted up to A only (the reference extracts K per fold, pls.cpp:477/531; its first A

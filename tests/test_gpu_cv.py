@@ -125,10 +125,10 @@ def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
 
 @pytest.mark.parametrize("N,K,M,A", [(2600, 2200, 2, 4), (900, 37, 3, 5), (640, 1030, 1, 3)])
 def test_two_lane_engine_equals_one_lane_and_the_oracle(ctx, N, K, M, A, monkeypatch):
-    """>= 512 folds run as two waves in flight (GEMM of one lane under the fold kernel of the other, persistent self-fed
-    TMA GEMM looping over > 148 work items); one lane on the context's stream is the A/B reference.  Folds are
-    independent and every kernel is deterministic, so the two schedules must agree bit for bit; a sample of folds is
-    checked against explicit refits by the oracle."""
+    """>= 512 folds run as two waves in flight (the persistent, pre-tiled DMMA product of one lane under the TMA-ring-fed
+    fold kernel of the other: cv_gemm.cu, cv.cu); one lane on the context's stream with the general GEMM is the A/B
+    reference.  Folds are independent, every kernel is deterministic and neither product splits the reduction axis, so
+    the two schedules must agree bit for bit; a sample of folds is checked against explicit refits by the oracle."""
     import os
     monkeypatch.setenv("PLSB_CV_NO_SMALL", "1")     # (the small shape would otherwise run as one launch out of shared memory)
     X, Y = port.synth(991, N, K, M, L=4)
