@@ -84,6 +84,8 @@ def test_c5s_loo(ctx):
                                            (70, 1024, 2, 6, 20, 6), (40, 1500, 5, 9, 1, 40),
                                            # 8 columns per thread (K <= 2048) with every M variant, ragged K
                                            (64, 1536, 8, 5, 2, 20), (48, 2048, 6, 4, 1, 30), (52, 1026, 4, 7, 5, 11),
+                                           # outside the fused kernel's range: K > 4096, 8 < M <= 32 at K >= 1024
+                                           (30, 4500, 2, 3, 1, 10), (44, 1100, 12, 4, 2, 9),
                                            # M > 32: per-fold scratch in global memory (step_wide.cuh)
                                            (80, 45, 36, 4, 3, 12), (60, 1100, 34, 3, 1, 10)])
 def test_cv_matches_oracle_and_fold_sharding(ctx, N, K, M, A, ts, nf):
