@@ -6,7 +6,7 @@ ARCH      := -gencode arch=compute_100a,code=sm_100a
 NVFLAGS   := $(ARCH) -O3 -std=c++17 -lineinfo -Xcompiler -fPIC -Xcompiler -Wall -Iinclude
 CSRC      := pls_b200/csrc
 CU        := $(CSRC)/api.cu $(CSRC)/dataset.cu $(CSRC)/pass.cu $(CSRC)/xty.cu $(CSRC)/scores.cu $(CSRC)/step.cu $(CSRC)/synth.cu $(CSRC)/gemm.cu $(CSRC)/allreduce.cu $(CSRC)/stats.cu \
-             $(CSRC)/fit.cu $(wildcard $(CSRC)/predict.cu) $(wildcard $(CSRC)/cv.cu) $(CSRC)/cv_small.cu $(CSRC)/cv_gemm.cu
+             $(CSRC)/fit.cu $(wildcard $(CSRC)/predict.cu) $(wildcard $(CSRC)/cv.cu) $(CSRC)/cv_small.cu $(CSRC)/cv_gemm.cu $(CSRC)/noalloc.cu
 OBJ       := $(patsubst $(CSRC)/%.cu,build/%.o,$(CU)) build/host_stats.o
 HDR       := $(wildcard $(CSRC)/*.h $(CSRC)/*.cuh) include/plsb.h
 LIB       := pls_b200/libplsb.so

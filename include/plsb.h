@@ -173,6 +173,23 @@ int plsb_cv_folds_press(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds
 /* mean / sst / stdev (each K, any may be NULL) of host column-major X; means_in (K or NULL): use these means */
 int plsb_colstats(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K, const double *means_in,
                   double *mean, double *sst, double *stdev);
+/* The same column statistics for callers that must not allocate device memory.  No counterpart in the reference.
+ * plsb_colstats needs a context (streams, pools) and allocates a staging copy of X plus scratch for its partial sums.
+ * A plug-in running inside an application that has already claimed the GPU's memory for its own arena, a call made from
+ * a latency-critical loop where cudaMalloc/cudaFree would stall every stream of the device, or code held to a
+ * "no allocations after start-up" budget cannot afford that.  This variant takes no context and calls no cudaMalloc,
+ * cudaFree or pool routine: the caller hands in DEVICE pointers it already owns — dX, the N x K matrix, column-major
+ * with leading dimension ldx >= N, and d_mean / d_sst / d_stdev, K doubles each, any of them NULL — plus the device
+ * ordinal and a cudaStream_t (as void *, NULL = default stream).  The kernels are queued on that stream and the call
+ * returns without synchronising; results are valid in stream order.  N < 2 gives sst = 0 like the reference.
+ * Limit: K <= 8192 (PLSB_ERR_ARG beyond it, nothing is launched; N is unbounded).  The partial sums live in a 4.06 MiB
+ * __device__ array compiled into the library, which every GPU that loads libplsb.so holds until the process exits.
+ * All calls on one GPU share that array: calls that may overlap on the GPU (two streams, two threads) race and
+ * must be ordered by the caller; back-to-back calls on one stream need nothing cleared between them.
+ * The first call on each device resolves the array's device address (cudaGetSymbolAddress) and caches it: make that
+ * call during initialisation, before starting any stream capture.  The caller's current device is restored. */
+int plsb_colstats_static(int device, void *stream, const double *dX, int64_t ldx, int64_t N, int64_t K,
+                         double *d_mean, double *d_sst, double *d_stdev);
 /* Z = (X - mean) / stdev by column; mean_in/stdev_in both NULL: computed from X (N-1 variance) */
 int plsb_colwise_z_scores(plsb_ctx_t ctx, const double *X, int64_t ldx, int64_t N, int64_t K, const double *mean_in,
                           const double *stdev_in, double *Z, int64_t ldz);

@@ -24,7 +24,7 @@ SYMBOLS = [
     "plsb_dataset_shape", "plsb_dataset_concat", "plsb_dataset_download", "plsb_dataset_set_sharded", "plsb_dataset_build_gram",
     "plsb_fit", "plsb_fit_resident", "plsb_model_download", "plsb_model_download_scores", "plsb_model_destroy", "plsb_fit_host", "plsb_xty", "plsb_xtx",
     "plsb_scores", "plsb_fitted", "plsb_predict_residuals", "plsb_coefficients", "plsb_sse_prefixes", "plsb_sse",
-    "plsb_cv_folds", "plsb_cv_folds_press", "plsb_colstats", "plsb_colwise_z_scores", "plsb_dataset_zscore",
+    "plsb_cv_folds", "plsb_cv_folds_press", "plsb_colstats", "plsb_colstats_static", "plsb_colwise_z_scores", "plsb_dataset_zscore",
     "plsb_normalcdf", "plsb_wilcoxon", "plsb_validation", "plsb_optimal_num_components", "plsb_lso_folds",
     "plsb_profile_enable", "plsb_profile_reset", "plsb_profile_get", "plsb_launch_count",
 ]
@@ -260,6 +260,15 @@ def colstats(ctx, X, means=None):
     mi = None if means is None else np.ascontiguousarray(means, dtype=np.float64)
     check(lib().plsb_colstats(ctx.h, P(X), i64(max(N, 1)), i64(N), i64(K), P(mi), P(mean), P(sst), P(sd)))
     return mean, sst, sd
+
+
+def colstats_static(device, stream, dX, ldx, N, K, d_mean=None, d_sst=None, d_stdev=None):
+    """plsb_colstats_static: the allocation-free variant.  Every pointer is a raw DEVICE address (int) that the caller
+    owns — the column-major N x K matrix and up to three K-vectors of results; `stream` is a cudaStream_t handle (0 =
+    default stream).  Nothing is copied or synchronised here: the results are ready in stream order."""
+    vp = lambda a: C.c_void_p(a) if a else None
+    check(lib().plsb_colstats_static(C.c_int(device), vp(stream), vp(dX), i64(ldx), i64(N), i64(K), vp(d_mean), vp(d_sst),
+                                     vp(d_stdev)))
 
 
 def colwise_z_scores(ctx, X, mean=None, stdev=None):
