@@ -167,21 +167,25 @@ void DeviceMirror::load_shards(const double *X, int64_t ldx, const double *Y, in
     }, "plsb_dataset_create(shard)");
 }
 
+void DeviceMirror::prepare() {
+    rehome();
+    source.clear();
+    for (plsb_dataset_t d : full)
+        if (d && source.empty()) source.push_back(d);
+    if (source.empty())
+        for (plsb_dataset_t d : shard)
+            if (d) source.push_back(d);
+}
+
 int DeviceMirror::ensure_full(size_t slot) {
     Engine &e = Engine::get();
     if (full[slot]) return PLSB_OK;
-    std::vector<plsb_dataset_t> src;
-    for (plsb_dataset_t d : full)
-        if (d && src.empty()) src.push_back(d);
-    if (src.empty())
-        for (plsb_dataset_t d : shard)
-            if (d) src.push_back(d);
-    if (src.empty()) return PLSB_ERR_ARG;   // a Model built without data (the reference's private constructors)
-    return plsb_dataset_concat(e.ctx[slot], (int64_t)src.size(), src.data(), &full[slot]);
+    if (source.empty()) return PLSB_ERR_ARG;   // a Model built without data (the reference's private constructors)
+    return plsb_dataset_concat(e.ctx[slot], (int64_t)source.size(), source.data(), &full[slot]);
 }
 
 plsb_dataset_t DeviceMirror::full_on(size_t slot) {
-    rehome();
+    prepare();
     ok(ensure_full(slot), "plsb_dataset_concat");
     return full[slot];
 }

@@ -65,14 +65,17 @@ struct DeviceMirror {
     void load_full(const double *X, int64_t ldx, const double *Y, int64_t ldy);
     void load_shards(const double *X, int64_t ldx, const double *Y, int64_t ldy);
     // the replica on `slot`, made from an existing copy if it is not there yet (call with Engine::mu held).
-    // prepare() on the calling thread first, then ensure_full(slot) may run on one worker per slot (returns a status).
-    void prepare() { rehome(); }
+    // prepare() on the calling thread first: it fixes the copy every missing replica will be made from (the first
+    // replica that exists, else the row shards).  Then ensure_full(slot) may run on one worker per slot (returns a
+    // status): a worker writes full[slot] only and never looks at its siblings' slots.
+    void prepare();
     int ensure_full(size_t slot);
     plsb_dataset_t full_on(size_t slot);
     void drop_shards();
     ~DeviceMirror();
 
   private:
+    std::vector<plsb_dataset_t> source;   // chosen by prepare(); read-only while workers run
     void rehome();   // after Engine::configure: carry the data over to the new contexts
 };
 

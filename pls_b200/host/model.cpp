@@ -261,10 +261,14 @@ Residual Model::cv_on_device(const std::vector<int64_t> &test_idx, size_t nfolds
     std::vector<double> E((size_t)(M * (int64_t)A * rows));
     const size_t ndev = std::min(e.ndev(), std::max<size_t>(nfolds, 1));
     mir.prepare();
+    // replicas first, on every GPU at once, device to device from the copy the fit left behind — and only then the
+    // folds: a replica made while its source GPU is already running folds would wait for that GPU's stream
+    if (ndev > 1)
+        e.parallel([&](size_t i) -> int { return i < ndev ? mir.ensure_full(i) : PLSB_OK; }, "plsb_dataset_concat");
     auto work = [&](size_t i) -> int {
         if (i >= ndev) return PLSB_OK;
         const int64_t f0 = (int64_t)(i * nfolds / ndev), f1 = (int64_t)((i + 1) * nfolds / ndev);
-        int rc = mir.ensure_full(i);   // replica on this GPU: device to device from the copy the fit left behind
+        int rc = mir.ensure_full(i);
         if (rc == PLSB_OK)
             rc = plsb_cv_folds(mir.full[i], (int64_t)A, meth, (int64_t)nfolds, (int64_t)test_size, test_idx.data(), f0, f1 - f0,
                                E.data());
