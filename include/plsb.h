@@ -46,7 +46,8 @@ int plsb_ctx_create(int device, plsb_ctx_t *ctx);
 int plsb_ctx_destroy(plsb_ctx_t ctx);
 int plsb_ctx_sync(plsb_ctx_t ctx);
 /* Device allocations are stream-ordered and cached in the device's memory pool between calls; this returns the
- * cache to the driver (e.g. before handing the GPU to another library). */
+ * cache to the driver (e.g. before handing the GPU to another library), and frees the pinned host staging buffers and
+ * host threads that large uploads / downloads of this context left behind (they come back with the next one). */
 int plsb_ctx_trim(plsb_ctx_t ctx);
 /* Row-sharded single fits: one context per process/GPU.  Rank 0 calls
  * plsb_comm_unique_id, the 128 bytes are broadcast by the caller's own plumbing

@@ -212,6 +212,10 @@ class Dataset:
                 if "T" in download:
                     out["T"] = np.zeros((N, A), order="F")
                 check(lib().plsb_model_download(mh, *[P(out.get(k)) for k in "WPRQT"]))
+                if "C" in download:   # the scores as the drop-in's Model::T takes them: (re, im) pairs, im = 0
+                    Tc = np.zeros((N, A), order="F", dtype=np.complex128)
+                    check(lib().plsb_model_download_scores(mh, Tc.ctypes.data_as(_dp), C.c_int(1)))
+                    out["C"] = Tc
         finally:
             lib().plsb_model_destroy(mh)
         return out

@@ -232,6 +232,8 @@ int plsb_ctx_trim(plsb_ctx_t c) {
     PLSB_ARG(c, "ctx is null");
     PLSB_CUDA(cudaSetDevice(c->device));
     PLSB_CUDA(cudaStreamSynchronize(c->stream));
+    PLSB_CUDA(cudaStreamSynchronize(c->copy_stream));
+    hstage_release(c);   // pinned staging buffers + host thread pool of large transfers: rebuilt on the next one
     cudaMemPool_t pool;
     PLSB_CUDA(cudaDeviceGetDefaultMemPool(&pool, c->device));
     PLSB_CUDA(cudaMemPoolTrimTo(pool, 0));

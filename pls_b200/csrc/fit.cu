@@ -128,6 +128,20 @@ static int download_scores(plsb_ctx *c, const double *Td, size_t n, double *T, b
     const bool pinned = cudaPointerGetAttributes(&pa, T) == cudaSuccess && pa.type == cudaMemoryTypeHost;
     cudaGetLastError();
     const char *off = getenv("PLSB_NO_STAGE");
+    if (as_complex && n * 8 < ((size_t)1 << 20)) {
+        // small models (the CLI's files, the one-launch CV cases): no pinned staging buffers, no host thread pool — the
+        // reals land in the upper half of the caller's (re, im) buffer and are spread out in place, front to back
+        // (pair j is written at 2j, 2j+1 <= n+j, i.e. never over a value that is still to be read)
+        if (n == 0) return PLSB_OK;
+        PLSB_CUDA(cudaMemcpyAsync(T + n, Td, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+        PLSB_CUDA(cudaStreamSynchronize(c->stream));
+        for (size_t j = 0; j < n; ++j) {
+            const double v = T[n + j];
+            T[2 * j] = v;
+            T[2 * j + 1] = 0.0;
+        }
+        return PLSB_OK;
+    }
     if (as_complex || (!pinned && n * 8 >= ((size_t)8 << 20) && !(off && *off == '1'))) return download_staged(c, Td, n, T, as_complex);
     PLSB_CUDA(cudaMemcpyAsync(T, Td, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
     return PLSB_OK;

@@ -249,3 +249,18 @@ def test_column_statistics_and_z_scores(ctx):
     Xc = rng.standard_normal((10, 4)); Xc[:, 2] = 3.0
     Z = _capi.colwise_z_scores(ctx, Xc)
     assert np.isnan(Z[:, 2]).all() and np.isfinite(Z[:, [0, 1, 3]]).all()
+
+
+def test_complex_scores_download_small_and_staged_and_after_trim(ctx):
+    """plsb_model_download_scores(as_complex=1) fills the drop-in's complex-typed Model::T (pls.h:251-254).  Below 1 MB it
+    widens in place in the caller's buffer (no pinned staging, no host threads); above, it goes through the staging
+    pipeline — and plsb_ctx_trim, which frees that pipeline's buffers, must leave the next large transfer working."""
+    rng = np.random.default_rng(31)
+    for N, A in [(50, 3), (1, 1), (70001, 2), (50, 3)]:        # 1.2 KB, 8 B, 1.12 MB (staged), small again
+        X = rng.standard_normal((N, 12)); Y = rng.standard_normal((N, 2))
+        ds = _capi.Dataset(ctx, X, Y)
+        out = ds.fit_resident(A, 0, download="TC")
+        assert np.array_equal(out["C"].real, out["T"]) and not out["C"].imag.any()
+        assert np.abs(out["T"]).max() > 0
+        ds.close()
+        ctx.trim()
