@@ -17,3 +17,11 @@ def pytest_configure(config):
 def golden():
     from tests.util import load_golden
     return load_golden
+
+
+def pytest_terminal_summary(terminalreporter):
+    """say when a fit passed on the extended-precision criterion rather than against the reference-pinned FP64 checker"""
+    from tests import util
+    for u in util.SECOND_CRITERION_USES:
+        terminalreporter.write_line("[parity] extended-precision criterion used: N,K,M,A=%s  CUDA-checker %.2e  CUDA-ext %.2e  "
+                                    "checker-ext %.2e" % (u["shape"], u["e_gw"], u["e_ge"], u["e_we"]))
