@@ -154,7 +154,11 @@ int plsb_sse(plsb_ctx_t ctx, const double *R, const double *Q, int64_t K, int64_
  * fold is the complement (cross products are order-independent up to rounding, so the reference's
  * training-row order does not need to be shipped).  Folds [fold0, fold0+nfolds_local) are computed
  * by this call (fold sharding across GPUs: no communication); E has `rows_total` = total folds *
- * test_size rows per (m, c) column and only this call's rows are written. */
+ * test_size rows per (m, c) column and only this call's rows are written.
+ * `method` is validated (0 or 1) and otherwise has no effect here: every fold is refitted from the downdated cross
+ * products X'X - X_H'X_H, X'Y - X_H'Y_H (the KERNEL_TYPE2 recurrence, pls.cpp:423-424), or with the KERNEL_TYPE1
+ * recurrence in the one-launch small-data kernel; the two give the same residuals to rounding (tests hold both to
+ * the reference's cv_LOO / cv_LSO fixtures at 1e-9). */
 int plsb_cv_folds(plsb_dataset_t ds, int64_t A, int method, int64_t nfolds_total, int64_t test_size,
                   const int64_t *test_idx, int64_t fold0, int64_t nfolds_local, double *E);
 /* Same folds, with validation's PRESS sums (pls.cpp:235-252: column sums of squared residuals) reduced ON THE DEVICE:
