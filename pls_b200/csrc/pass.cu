@@ -572,14 +572,14 @@ int launch_fused_pass(plsb_ctx *c, const plsb_dataset *ds, const double *r, doub
     if (ldk <= 512) return run_fused<256, 256, 2, 8>(c, ds, r, out, t_out, across_ranks);
     if (ldk <= 1024) return run_fused<256, 256, 4, 4>(c, ds, r, out, t_out, across_ranks);
     if (ldk <= 2048) {
-        // Large streams: ONE 512-thread CTA per SM (two row groups of 2 rows each) behind a three-tile ring.  Small
-        // ones: two 256-thread CTAs per SM, 4 rows per thread, one tile each.  Measured on C4 at the ~1.4-1.5 GHz a
-        // power-capped board sustains under this stream: 2.30 ms vs 2.49 ms per pass (the single CTA re-arms its ring
-        // as soon as a tile is in registers and 16 warps share the arithmetic); at 1.73 GHz the two are within 1 %.
-        // (Row shards of a multi-GPU fit are smaller, spend a larger share of the time in the latency-bound kernels
-        // between the passes and keep a higher clock: measured at 4 GB and 2 GB per GPU the two-CTA shape is 6-8 %
-        // faster, at 8 GB and 16 GB the one-CTA shape is 3-7 % faster — hence the size threshold.)
-        const bool big = ds->N * ldk >= 3 * ((int64_t)1 << 28) && !getenv("PLSB_PASS_CTAS_PER_SM");
+        // Streams of 2 GB and more: ONE 512-thread CTA per SM (two row groups of 2 rows each) behind a three-tile ring.
+        // Smaller ones: two 256-thread CTAs per SM, 4 rows per thread, one tile each.  Measured under SUSTAINED load
+        // (tools/devbench_shape.py, 3 s per cell, board at its 1000 W cap, profiles/r3p_shape.log), ms per 32-component fit,
+        // one-CTA vs two-CTA: 2 GB 11.14 / 11.24, 4 GB 20.2 / 21.8, 8 GB 39.9 / 42.8, 16 GB 79.6 / 84.8 — the single CTA
+        // re-arms its ring as soon as a tile is in registers, 16 warps share the arithmetic, and it draws less power per
+        // byte, which is what counts once the cap sets the clock.  (Round 2 put the threshold at 6.4 GB after short runs
+        // in which 2-4 GB shards had not yet reached the cap; the driver's 4-GPU run then lost 6 % on it.)
+        const bool big = ds->N * ldk >= ((int64_t)240 << 20) && !getenv("PLSB_PASS_CTAS_PER_SM");
         if (rbsel == 2) return run_fused<256, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
         if (rbsel == 12 || (rbsel == 0 && big)) return run_fused<512, 256, 8, 2>(c, ds, r, out, t_out, across_ranks);
         return run_fused<256, 256, 8, 4>(c, ds, r, out, t_out, across_ranks);
