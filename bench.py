@@ -531,7 +531,8 @@ def run_ours(args):
     # ---- end to end through the public API with HOST buffers (upload + fit + results back) --------------
     e2e = None
     if not args.no_e2e:
-        Xh = torch.empty((K, rows), dtype=torch.float64).pin_memory().numpy().T      # column-major rows x K
+        Xh_t = torch.empty((K, rows), dtype=torch.float64).pin_memory()
+        Xh = Xh_t.numpy().T                                                          # column-major rows x K
         Yh = torch.empty((M, rows), dtype=torch.float64).pin_memory().numpy().T
         _capi.check(_capi.lib().plsb_dataset_download(ds.h, _capi.P(Xh), _capi.i64(rows), _capi.P(Yh), _capi.i64(rows)))
         ds.close()
@@ -566,6 +567,34 @@ def run_ours(args):
                                    "fit_after_upload": fit_ms / max(nf, 1), "of_which_scores_T": sc_ms / max(nf, 1)},
                "path": ("X'X and X'Y accumulated on the tensor cores while the rows cross PCIe; components from the "
                         "L2-resident X'X; one DMMA pass T = X R") if npf == 0 else "streaming passes (one read of X per component)"}
+
+        # the denominator of the end-to-end figure: what this box's PCIe / host memory gives when every rank copies its
+        # pinned shard to its GPU at the same time and nothing else runs (no kernels, no packing, no results back)
+        try:
+            dbuf = torch.empty((K, rows), dtype=torch.float64, device="cuda")
+            dbuf.copy_(Xh_t, non_blocking=True); torch.cuda.synchronize()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(2):
+                dbuf.copy_(Xh_t, non_blocking=True)
+            torch.cuda.synchronize()
+            barrier()
+            copy_s = (time.perf_counter() - t0) / 2
+            del dbuf
+            if dist is not None:
+                t = torch.tensor([copy_s], device="cuda", dtype=torch.float64)
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                copy_s = t.item()
+            floor_s = copy_s * (K + M) / K                        # X and Y
+            e2e["h2d_floor_ms"] = floor_s * 1e3
+            e2e["h2d_floor_GBps_per_rank"] = 8.0 * rows * K / copy_s / 1e9
+            e2e["frac_of_h2d_floor"] = floor_s / e2e_s
+            e2e["h2d_floor_what"] = (f"{world} concurrent cudaMemcpyAsync of each rank's pinned X shard ({8.0 * rows * K / 1e9:.2f} GB), "
+                                     "max over ranks, scaled to X and Y; frac_of_h2d_floor = floor / measured e2e step")
+        except Exception as e:
+            e2e["h2d_floor_ms"] = None
+            e2e["h2d_floor_what"] = repr(e)
+        del Xh_t
 
     # ---- config 5: full leave-one-out CV, 20 000 fits of 20000 x 4096 (A = 64), folds sharded over the ranks -----
     cv = None

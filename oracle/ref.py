@@ -126,6 +126,11 @@ class Model:
         self._lib.plsref_cv_lso(self.h, C.c_double(frac), i64(trials), C.c_uint32(seed), P(E))
         return E.transpose(0, 2, 1)
 
+    def cv_lso_rng_after(self, frac, trials, seed=5489):
+        """the next output of the caller's std::mt19937 after the reference's cv_LSO has drawn its folds from it"""
+        self._lib.plsref_cv_lso_rng_after.restype = C.c_uint32
+        return int(self._lib.plsref_cv_lso_rng_after(self.h, C.c_double(frac), i64(trials), C.c_uint32(seed)))
+
     def cv_new_data(self, Xn, Yn):
         Xn, Yn = F(Xn), F(Yn)
         E = np.zeros((self.M, self.A, Xn.shape[0]))

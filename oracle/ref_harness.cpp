@@ -155,6 +155,15 @@ void plsref_lso_folds(int64_t N, double frac, int64_t trials, uint32_t seed, int
     }
 }
 
+// What the caller's generator yields next after cv_LSO(frac, trials, rng) returns: cv_LSO takes `rng` by reference
+// (pls.cpp:512) and advances it by one rand_nchoosek per trial (pls.cpp:534).  The Model is the reference's own; the
+// residuals are discarded.
+uint32_t plsref_cv_lso_rng_after(void *h, double frac, int64_t trials, uint32_t seed) {
+    std::mt19937 rng(seed);
+    static_cast<Model *>(h)->cv_LSO(frac, trials, rng);
+    return (uint32_t)rng();
+}
+
 // Per-fold refit with the reference's own plsr, but with A (not K) inner components — the
 // residuals for the first A components are bit-identical. Explicit fold lists:
 // test_idx[nfolds*test_size]; train_idx[nfolds*train_size] (NULL => ascending complement, LOO order).

@@ -5,6 +5,7 @@ tests/cpp/api_check is a small program written the way a user of the reference w
 (PLS::Model, cv_LOO, validation, optimal_num_components ...); it dumps every result as a PLSBMAT1 file.
 The binaries are built in the build container (Eigen headers are not in this repo) and travel with the
 snapshot."""
+import json
 import os
 import re
 import struct
@@ -98,6 +99,9 @@ def test_cpp_model_api_matches_reference(tmp_path, name, A, method, trials):
             assert relerr(lso[:, -n:], g["lso_last"]) <= RTOL
         assert relerr(d["lso_ress"], g["lso_ress"]) <= RTOL
         assert np.array_equal(d["lso_opt"].ravel().astype(int), g["lso_opt"].astype(int))
+        # cv_LSO takes the caller's generator by reference and must leave it where the reference does (pls.cpp:512, 534)
+        want_rng = json.load(open(os.path.join(ROOT, "tests", "golden", "lso_rng_after.json")))[f"{name}:{trials}"]
+        assert int(d["rng_after"].ravel()[0]) == want_rng
     if "new_data" in g and method == 0:
         assert relerr(stacked(d, "newdata", M), g["new_data"]) <= RTOL
     # refit on row-reversed data: the regression is invariant to the order of the observations

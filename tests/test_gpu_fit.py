@@ -264,3 +264,18 @@ def test_complex_scores_download_small_and_staged_and_after_trim(ctx):
         assert np.abs(out["T"]).max() > 0
         ds.close()
         ctx.trim()
+
+
+@pytest.mark.parametrize("method", [0, 1])
+@pytest.mark.parametrize("N,K,M", [(8, 12, 2), (5, 9, 1), (6, 20, 3)])
+def test_components_past_the_numerical_rank(ctx, N, K, M, method):
+    """The 3-argument constructor asks for A = K components (pls.cpp:356-359); with K > N the data have rank N and the
+    reference's components N+1..K are finite garbage (a deflated cross product of rounding noise, normalised: loadings
+    up to 1e15).  The first N components are still the model, held to 1e-9; the rest must stay finite like the reference's."""
+    X, Y = port.synth(77 + N, N, K, M, L=3)
+    want = port.fit(X, Y, K, method)
+    got = _capi.fit_host(ctx, X, Y, K, method)
+    head = lambda st: {k: (None if st.get(k) is None else st[k][:, :N]) for k in "WPRQT"}
+    assert_state_close(head(got), head(want))
+    for k in "WPRQ":
+        assert np.isfinite(got[k]).all(), k
