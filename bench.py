@@ -731,6 +731,19 @@ def run_ours(args):
         if e2e is not None and e2e_cpp and "fit_c4" in e2e_cpp and "model_ctor_s_mean" in e2e_cpp["fit_c4"]:
             e2e["cpp_model_ctor_fits_per_s"] = 1.0 / e2e_cpp["fit_c4"]["model_ctor_s_mean"]
 
+    # the same drop-in on ALL the GPUs of the run: ONE C++ process, PLSB_DEVICES=0..N-1, rows sharded by the engine's own
+    # threads + peer exchange (host/model.cpp) — what a C++ caller of PLS::Model gets on this box.  The torchrun ranks
+    # give the GPUs' memory back and wait at a barrier while rank 0 runs it.
+    if world > 1 and not args.no_e2e:
+        ctx.trim()
+        torch.cuda.empty_cache()
+        barrier()
+        if rank == 0:
+            e2e_cpp = cpp_dropin_legs(C4, C5, ",".join(str(i) for i in range(world)), with_cv=False)
+            if e2e is not None and e2e_cpp and "fit_c4" in e2e_cpp and "model_ctor_s_mean" in e2e_cpp["fit_c4"]:
+                e2e["cpp_model_ctor_fits_per_s"] = 1.0 / e2e_cpp["fit_c4"]["model_ctor_s_mean"]
+        barrier()
+
     # CPU baselines come last: sixteen busy host threads right before a latency-bound GPU leg slow its launches down
     if cv is not None and rank == 0 and world == 1 and not args.no_cpu:
         try:
