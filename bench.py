@@ -265,7 +265,7 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
-def cpp_dropin_legs(c4, c5, device, with_cv=True):
+def cpp_dropin_legs(c4, c5, device, with_cv=True, timeout=900):
     """tests/cpp/api_bench: the C++ drop-in API on pageable Eigen matrices, timed with the host clock inside the program."""
     exe = os.path.join(ROOT, "tests", "cpp", "api_bench")
     if not os.path.exists(exe):
@@ -277,7 +277,7 @@ def cpp_dropin_legs(c4, c5, device, with_cv=True):
         jobs.append(("loo_c5", ["loo", c5["N"], c5["K"], c5["M"], c5["A"], 1, c5["seed"], c5["L"]]))
     for name, argv in jobs:
         try:
-            r = subprocess.run([exe] + [str(a) for a in argv], capture_output=True, text=True, timeout=900, env=env)
+            r = subprocess.run([exe] + [str(a) for a in argv], capture_output=True, text=True, timeout=timeout, env=env)
             out[name] = json.loads(r.stdout.strip().splitlines()[-1]) if r.returncode == 0 else {"error": r.stderr[-500:]}
         except Exception as e:
             out[name] = {"error": repr(e)}
@@ -734,12 +734,12 @@ def run_ours(args):
     # the same drop-in on ALL the GPUs of the run: ONE C++ process, PLSB_DEVICES=0..N-1, rows sharded by the engine's own
     # threads + peer exchange (host/model.cpp) — what a C++ caller of PLS::Model gets on this box.  The torchrun ranks
     # give the GPUs' memory back and wait at a barrier while rank 0 runs it.
-    if world > 1 and not args.no_e2e:
+    if world > 1 and not args.no_e2e and args.e2e_cpp_multi:
         ctx.trim()
         torch.cuda.empty_cache()
         barrier()
         if rank == 0:
-            e2e_cpp = cpp_dropin_legs(C4, C5, ",".join(str(i) for i in range(world)), with_cv=False)
+            e2e_cpp = cpp_dropin_legs(C4, C5, ",".join(str(i) for i in range(world)), with_cv=False, timeout=240)
             if e2e is not None and e2e_cpp and "fit_c4" in e2e_cpp and "model_ctor_s_mean" in e2e_cpp["fit_c4"]:
                 e2e["cpp_model_ctor_fits_per_s"] = 1.0 / e2e_cpp["fit_c4"]["model_ctor_s_mean"]
         barrier()
@@ -806,6 +806,8 @@ def main():
     ap.add_argument("--no-xtx", action="store_true")
     ap.add_argument("--no-loo-c4", action="store_true", help="skip the 1,000,000-fold LOO on the C4 matrix (~10 s on one GPU)")
     ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--e2e-cpp-multi", action="store_true",
+                    help="N > 1: also time the C++ drop-in (one process, PLSB_DEVICES=0..N-1) while the ranks wait at a barrier")
     ap.add_argument("--write-fixtures", action="store_true",
                     help="N = 1 only: write gpurun_out/c4_loo_press.json (the PRESS fixture the loo_c4 parity check reads)")
     ap.add_argument("--ref-rows", type=int, default=C4["N"],

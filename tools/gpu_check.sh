@@ -4,6 +4,7 @@
 #   tag   prefix of the files written under gpurun_out/ (e.g. r3x)
 #   N     GPUs (default 1); N > 1 runs bench.py under torchrun, one rank per GPU
 #   what  any of: tests multi smoke bench reference midcv shape   (default: tests smoke bench)
+#   BENCH_FLAGS (environment): extra bench.py flags, e.g. BENCH_FLAGS=--e2e-cpp-multi
 # Every step runs under its own timeout and writes <tag>_<step>[_nN].log / .json plus its exit code.
 TAG=${1:?usage: tools/gpu_check.sh <tag> [N] [what...]}; N=${2:-1}; shift; shift
 WHAT=${*:-tests smoke bench}
@@ -16,7 +17,7 @@ for w in $WHAT; do
     smoke)     timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > ${O}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a ${O}_smoke.log ;;
     bench)     if [ "$N" -gt 1 ]; then
                  timeout 1500 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
-                     bench.py --gpus $N --steps 20 --warmup 3 > ${O}_bench_n$N.json 2> ${O}_bench_n$N.err
+                     bench.py --gpus $N --steps 20 --warmup 3 $BENCH_FLAGS > ${O}_bench_n$N.json 2> ${O}_bench_n$N.err
                else
                  timeout 1500 python bench.py --steps 20 --warmup 3 > ${O}_bench_n1.json 2> ${O}_bench_n1.err
                fi; echo "bench rc=$?" ;;
